@@ -1,0 +1,190 @@
+/* Oracle (TEST INFRASTRUCTURE, not product code): plain-C restatement of the optical-flow hot path.
+ *
+ * Built by oracle/Makefile with  gcc -O2 -ffp-contract=off  so that every fp32 operation is
+ * rounded exactly once, in the order written here.  Only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline leg may load the resulting library.
+ *
+ * Algorithms restated (reference = /root/reference):
+ *   orc_corr_volume      corr[b,p,q] = <f1[b,:,p], f2[b,:,q]> / sqrt(C)
+ *                        call site nnunet/network_architecture/SegFlowGaussian.py:929; arithmetic of
+ *                        torchvision models/optical_flow/raft.py:424-431 (RAFT core/corr.py identical)
+ *   orc_avg_pool2x2      F.avg_pool2d(x, 2, stride=2), floor mode          (raft.py:387-392)
+ *   orc_lookup           radius-r bilinear window lookup over the pyramid    (raft.py:394-422,
+ *                        _utils.py:8-19; ATen grid_sampler, align_corners=True, zero padding)
+ *   orc_warp2d           SpatialTransformer.forward                         (nnunet/network_architecture/
+ *                        integration.py:61-79)
+ *   orc_warp_onehot_argmax  one_hot -> warp -> argmax                       (SegFlowGaussian.py:3571-3580)
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ORC_API __attribute__((visibility("default")))
+
+/* ---- coordinate sequences (must stay un-contracted: compile with -ffp-contract=off) ---- */
+static inline float lookup_coord(float p, int size) {
+    float s1 = (float)(size - 1);
+    float n = (2.0f * p) / s1 - 1.0f;            /* RAFT bilinear_sampler normalisation          */
+    return ((n + 1.0f) / 2.0f) * s1;             /* ATen grid_sampler_unnormalize, align_corners */
+}
+
+static inline float warp_coord(float p, int size) {
+    float s1 = (float)(size - 1);
+    float n = 2.0f * (p / s1 - 0.5f);            /* integration.py:68 */
+    return ((n + 1.0f) / 2.0f) * s1;
+}
+
+static inline float fetch(const float* img, int h, int w, int y, int x) {
+    return (y >= 0 && y < h && x >= 0 && x < w) ? img[(size_t)y * w + x] : 0.0f;
+}
+
+/* ATen order: nw, ne, sw, se */
+static inline float bilinear(const float* img, int h, int w, float uy, float ux) {
+    float fx = floorf(ux), fy = floorf(uy);
+    int x0 = (int)fx, y0 = (int)fy;
+    float wxh = ux - fx, wxl = (fx + 1.0f) - ux;
+    float wyh = uy - fy, wyl = (fy + 1.0f) - uy;
+    /* ATen's CUDA grid_sampler accumulates `out += val * weight`, which nvcc contracts to FMA; the reference
+     * ran on a GPU, so the restatement uses fmaf explicitly (the weight products are plain multiplies). */
+    float acc = fetch(img, h, w, y0, x0) * (wxl * wyl);
+    acc = fmaf(fetch(img, h, w, y0, x0 + 1), wxh * wyl, acc);
+    acc = fmaf(fetch(img, h, w, y0 + 1, x0), wxl * wyh, acc);
+    acc = fmaf(fetch(img, h, w, y0 + 1, x0 + 1), wxh * wyh, acc);
+    return acc;
+}
+
+ORC_API void orc_corr_volume(const float* f1, const float* f2, int B, int C, int HW, float* out) {
+    const float div = sqrtf((float)C);
+
+    for (int b = 0; b < B; ++b)
+        for (int p = 0; p < HW; ++p) {
+            float* row = out + ((size_t)b * HW + p) * HW;
+            for (int q = 0; q < HW; ++q) row[q] = 0.0f;
+            for (int c = 0; c < C; ++c) {
+                const float a = f1[((size_t)b * C + c) * HW + p];
+                const float* f2c = f2 + ((size_t)b * C + c) * HW;
+                for (int q = 0; q < HW; ++q) row[q] = row[q] + a * f2c[q];
+            }
+            for (int q = 0; q < HW; ++q) row[q] = row[q] / div;
+        }
+}
+
+ORC_API void orc_avg_pool2x2(const float* in, long N, int h, int w, float* out) {
+    const int h2 = h / 2, w2 = w / 2;
+
+    for (long n = 0; n < N; ++n) {
+        const float* src = in + (size_t)n * h * w;
+        float* dst = out + (size_t)n * h2 * w2;
+        for (int y = 0; y < h2; ++y)
+            for (int x = 0; x < w2; ++x) {
+                float s = src[(size_t)(2 * y) * w + 2 * x];
+                s = s + src[(size_t)(2 * y) * w + 2 * x + 1];
+                s = s + src[(size_t)(2 * y + 1) * w + 2 * x];
+                s = s + src[(size_t)(2 * y + 1) * w + 2 * x + 1];
+                dst[(size_t)y * w2 + x] = s / 4.0f;
+            }
+    }
+}
+
+/* pyramid[l] -> [B*H*W, h_l, w_l] with h_l = h_{l-1} / 2.  coords [B,2,H,W] (ch0 = x).  out [B, L*K, H, W].
+ * taps (optional, may be NULL): per level, per query, per window index: ux[9] uy[9] -> float [L][N][2][side],
+ * idx (optional): int32 [L][N][2][side] = floor of those. */
+ORC_API void orc_lookup(const float* const* pyramid, const float* coords, int B, int H, int W, int L, int r,
+                        float* out, float* taps, int32_t* idx) {
+    const int side = 2 * r + 1, K = side * side, HW = H * W;
+    const long N = (long)B * HW;
+    int hl = H, wl = W;
+    for (int l = 0; l < L; ++l) {
+        const float scale = (float)(1 << l);
+
+        for (long n = 0; n < N; ++n) {
+            const int b = (int)(n / HW), p = (int)(n % HW);
+            const float cx = coords[((size_t)b * 2 + 0) * HW + p] / scale;
+            const float cy = coords[((size_t)b * 2 + 1) * HW + p] / scale;
+            const float* img = pyramid[l] + (size_t)n * hl * wl;
+            float ux[64], uy[64];
+            for (int i = 0; i < side; ++i) {
+                const float d = (float)(i - r);
+                ux[i] = lookup_coord(cx + d, wl);
+                uy[i] = lookup_coord(cy + d, hl);
+                if (taps) {
+                    taps[(((size_t)l * N + n) * 2 + 0) * side + i] = ux[i];
+                    taps[(((size_t)l * N + n) * 2 + 1) * side + i] = uy[i];
+                }
+                if (idx) {
+                    idx[(((size_t)l * N + n) * 2 + 0) * side + i] = (int32_t)floorf(ux[i]);
+                    idx[(((size_t)l * N + n) * 2 + 1) * side + i] = (int32_t)floorf(uy[i]);
+                }
+            }
+            for (int i = 0; i < side; ++i)
+                for (int j = 0; j < side; ++j)
+                    out[((size_t)b * L * K + (size_t)l * K + i * side + j) * HW + p] =
+                        bilinear(img, hl, wl, uy[j], ux[i]);
+        }
+        hl /= 2;
+        wl /= 2;
+    }
+}
+
+/* flow [B,2,H,W]: ch0 = row displacement, ch1 = column displacement.  mode 0 = bilinear, 1 = nearest. */
+ORC_API void orc_warp2d(const float* flow, const float* src, int B, int C, int H, int W, int mode, float* out,
+                        float* taps /* optional [B,2,H,W]: uy, ux */) {
+    const size_t HW = (size_t)H * W;
+
+    for (int b = 0; b < B; ++b)
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                const size_t pix = (size_t)y * W + x;
+                const float uy = warp_coord((float)y + flow[((size_t)b * 2 + 0) * HW + pix], H);
+                const float ux = warp_coord((float)x + flow[((size_t)b * 2 + 1) * HW + pix], W);
+                if (taps) {
+                    taps[((size_t)b * 2 + 0) * HW + pix] = uy;
+                    taps[((size_t)b * 2 + 1) * HW + pix] = ux;
+                }
+                for (int c = 0; c < C; ++c) {
+                    const float* img = src + ((size_t)b * C + c) * HW;
+                    float v;
+                    if (mode == 0) {
+                        v = bilinear(img, H, W, uy, ux);
+                    } else { /* ATen nearest: nearbyint (round half to even) */
+                        v = fetch(img, H, W, (int)nearbyintf(uy), (int)nearbyintf(ux));
+                    }
+                    out[((size_t)b * C + c) * HW + pix] = v;
+                }
+            }
+}
+
+ORC_API void orc_warp_onehot_argmax(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
+                                    int64_t* out) {
+    const size_t HW = (size_t)H * W;
+
+    for (int b = 0; b < B; ++b)
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                const size_t pix = (size_t)y * W + x;
+                const float uy = warp_coord((float)y + flow[((size_t)b * 2 + 0) * HW + pix], H);
+                const float ux = warp_coord((float)x + flow[((size_t)b * 2 + 1) * HW + pix], W);
+                const float fx = floorf(ux), fy = floorf(uy);
+                const int x0 = (int)fx, y0 = (int)fy;
+                const float wxh = ux - fx, wxl = (fx + 1.0f) - ux, wyh = uy - fy, wyl = (fy + 1.0f) - uy;
+                const float wt[4] = {wxl * wyl, wxh * wyl, wxl * wyh, wxh * wyh};
+                const int ty[4] = {y0, y0, y0 + 1, y0 + 1}, tx[4] = {x0, x0 + 1, x0, x0 + 1};
+                const int64_t* lab = label + (size_t)b * HW;
+                int64_t best = 0;
+                float bestv = -INFINITY;
+                for (int c = 0; c < num_classes; ++c) {
+                    float acc = 0.0f;
+                    for (int t = 0; t < 4; ++t) {
+                        float v = 0.0f;
+                        if (ty[t] >= 0 && ty[t] < H && tx[t] >= 0 && tx[t] < W)
+                            v = (lab[(size_t)ty[t] * W + tx[t]] == c) ? 1.0f : 0.0f;
+                        acc = acc + v * wt[t];
+                    }
+                    if (acc > bestv) { bestv = acc; best = c; }   /* first maximum wins, as torch.argmax */
+                }
+                out[(size_t)b * HW + pix] = best;
+            }
+}
+
+ORC_API int orc_version(void) { return 1; }

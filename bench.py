@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""Benchmark of the optical-flow hot path: frame-pairs/sec for (correlation pyramid build + 12 lookups + warp).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg4] [--graph]
+
+One "step" = one (patient, slice) cine unit of BASELINE.json configs[1]: 29 consecutive frame pairs with
+256-channel 32x32 feature maps -> CorrBlock build (batched over the 29 pairs), 12 CorrBlock lookups, and the
+29 SpatialTransformer warps of the 256x256 frames.  Data is synthetic (seed 1002).
+For N > 1 (torchrun, one rank per GPU) every rank runs its own unit per step: weak scaling, no data-path
+collective (the path shards by (patient, slice)); time is the max over ranks.
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput; `e2e` = the same metric through the
+public module API with pinned HOST buffers (H2D of every input + D2H of every output inside the timed
+region); `roofline` = the dominant kernel (the lookup) against the measured HBM peak; `cpu_baseline` = the
+oracle (torch CPU kernels, the ATen ops the reference's Python dispatches to) on a bounded sample.
+`--impl reference` times that CPU implementation alone (the reference arm).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: pairs, C, fmap H, W, image H, W
+    "cfg2": dict(pairs=29, C=256, H=32, W=32, IH=256, IW=256,
+                 desc="configs[1]: 29 frame pairs, 256-ch fmaps 32x32 (256^2 input), 4 levels, r=4, 12 lookups, 29 warps"),
+    "cfg4": dict(pairs=64, C=256, H=64, W=64, IH=512, IW=512,
+                 desc="configs[3]: 64 frame pairs, 256-ch fmaps 64x64, materialised volume, 12 lookups, 64 warps"),
+}
+ITERS, LEVELS, RADIUS = 12, 4, 4
+METRIC = "frame-pairs/sec (corr+12-iter lookup+warp, 256^2)"
+
+
+# ------------------------------------------------------------------------------------------------ data
+def make_unit(wl, seed, device="cpu", pin=False):
+    """Synthetic cine unit (SURVEY.md 8(d) cfg 2 recipe): consecutive frames are shifted/noisy copies."""
+    g = torch.Generator().manual_seed(seed)
+    P, C, H, W, IH, IW = wl["pairs"], wl["C"], wl["H"], wl["W"], wl["IH"], wl["IW"]
+    base = torch.randn(C, H, W, generator=g)
+    frames = [base]
+    for t in range(P):
+        frames.append(torch.roll(frames[-1], shifts=(t % 3 - 1, 1), dims=(1, 2)) + 0.1 * torch.randn(C, H, W, generator=g))
+    frames = torch.stack(frames)
+    f1, f2 = frames[:-1].contiguous(), frames[1:].contiguous()
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    grid = torch.stack([xs, ys]).float()[None].repeat(P, 1, 1, 1)
+    coords, cur = [], grid.clone()
+    for k in range(ITERS):
+        coords.append(cur.clone())
+        cur = cur + torch.randn(P, 2, H, W, generator=g) * 0.5
+        cur[:, 0].clamp_(-4, W + 4)
+        cur[:, 1].clamp_(-4, H + 4)
+    coords = torch.stack(coords)                                   # [12, P, 2, H, W]
+    img = torch.rand(P, 1, IH, IW, generator=g)
+    flow = torch.nn.functional.interpolate(torch.randn(P, 2, 9, 9, generator=g) * 3.0, size=(IH, IW),
+                                           mode="bicubic", align_corners=True).contiguous()
+    unit = dict(f1=f1, f2=f2, coords=coords, img=img, flow=flow)
+    if pin:
+        unit = {k: v.pin_memory() for k, v in unit.items()}
+    if device != "cpu":
+        unit = {k: v.to(device) for k, v in unit.items()}
+    return unit
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop_flag, self.thread = [], set(), False, None
+        self.max_mhz, self.ok = None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = str(e)
+
+    def _reasons(self):
+        nv = self.nv
+        fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        mask = fn(self.h)
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
+        return {n for bit, n in names.items() if mask & bit}
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                self.reasons |= self._reasons()
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.002)
+
+    def start(self):
+        if self.ok:
+            self.thread = threading.Thread(target=self._run, daemon=True)
+            self.thread.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join()
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "no NVML samples"}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_pairs_per_sec(wl, sample_pairs, budget_s=12.0, threads=None):
+    """The reference's CPU path (oracle: torch CPU kernels) on `sample_pairs` pairs of the workload."""
+    from oracle import corr_oracle, warp_oracle
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    unit = make_unit(dict(wl, pairs=sample_pairs), seed=1002)
+    st = warp_oracle.SpatialTransformer((wl["IH"], wl["IW"]))
+
+    def run():
+        # per pair, like the reference's frame loop (SegFlowGaussian.py:907-954): a CorrBlock per pair
+        for p in range(sample_pairs):
+            blk = corr_oracle.CorrBlock(unit["f1"][p:p + 1], unit["f2"][p:p + 1], num_levels=LEVELS, radius=RADIUS)
+            for k in range(ITERS):
+                blk(unit["coords"][k, p:p + 1])
+            st(flow=unit["flow"][p:p + 1], original=unit["img"][p:p + 1])
+
+    with torch.no_grad():
+        run()
+        best, t_start, reps = float("inf"), time.perf_counter(), 0
+        while reps < 3 or (time.perf_counter() - t_start < budget_s and reps < 50):
+            t0 = time.perf_counter()
+            run()
+            best = min(best, time.perf_counter() - t0)
+            reps += 1
+    return sample_pairs / best, threads, reps
+
+
+def run_reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = 4 if args.workload == "cfg2" else 1
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    from oracle import corr_oracle, warp_oracle
+    unit = make_unit(dict(wl, pairs=sample), seed=1002)
+    st = warp_oracle.SpatialTransformer((wl["IH"], wl["IW"]))
+
+    def step():
+        for p in range(sample):
+            blk = corr_oracle.CorrBlock(unit["f1"][p:p + 1], unit["f2"][p:p + 1], num_levels=LEVELS, radius=RADIUS)
+            for k in range(ITERS):
+                blk(unit["coords"][k, p:p + 1])
+            st(flow=unit["flow"][p:p + 1], original=unit["img"][p:p + 1])
+
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step()
+        dt = time.perf_counter() - t0
+    value = sample * args.steps / dt
+    sample_desc = f"{sample} of {wl['pairs']} pairs per step (per-pair CorrBlock + 12 lookups + 1 warp), torch CPU fp32"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "sample": sample_desc},
+        "cpu_baseline": {"value": value, "unit": "frame-pairs/s", "cores": threads, "kind": "port", "sample": sample_desc},
+        "e2e": {"value": value, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="auto", choices=["auto", "tf32", "fp32"])
+    ap.add_argument("--graph", action="store_true", help="replay each step as one CUDA graph")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    if args.impl == "reference":
+        return run_reference_arm(args, wl)
+
+    import cardioflow_b200 as cf
+    from cardioflow_b200 import _cabi
+    from oracle import corr_oracle as oracle_meta   # byte/flop formulas only (no compute)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        sys.exit("bench.py needs a CUDA device: the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    _cabi.lib()  # fail loudly if the extension is missing
+
+    P, C, H, W, IH, IW = wl["pairs"], wl["C"], wl["H"], wl["W"], wl["IH"], wl["IW"]
+    K81 = LEVELS * (2 * RADIUS + 1) ** 2
+    n_sets = 3
+    sets = [make_unit(wl, seed=1002 + 17 * rank + s, device=dev) for s in range(n_sets)]
+    lib = _cabi.lib()
+    pyr_floats = lib.cf_corr_pyramid_bytes(P, H, W, LEVELS) // 4
+    pyramid = torch.empty(pyr_floats, dtype=torch.float32, device=dev)
+    outs = torch.empty(ITERS, P, K81, H, W, dtype=torch.float32, device=dev)
+    warped = torch.empty(P, 1, IH, IW, dtype=torch.float32, device=dev)
+    st = cf.SpatialTransformer((IH, IW)).to(dev)
+    ev_l0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev_l1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+
+    def step(u, ev=None):
+        blk = cf.CorrBlock(u["f1"], u["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                           pyramid_buffer=pyramid)
+        if ev:
+            ev[0].record()
+        for k in range(ITERS):
+            blk(u["coords"][k], out=outs[k])
+        if ev:
+            ev[1].record()
+        cf.warp(u["img"], u["flow"], out=warped)
+        return blk
+
+    with torch.no_grad():
+        blk = step(sets[0])
+        used_precision = blk.used_precision
+        torch.cuda.synchronize()
+        graphs = None
+        if args.graph:
+            graphs = []
+            for u in sets:
+                gph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gph):
+                    step(u)
+                graphs.append(gph)
+
+        def run_step(i, ev=None):
+            if graphs:
+                graphs[i % n_sets].replay()
+            else:
+                step(sets[i % n_sets], ev)
+
+        for i in range(args.warmup):
+            run_step(i)
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        t_begin.record()
+        for i in range(args.steps):
+            run_step(i, None if graphs else (ev_l0[i], ev_l1[i]))
+        t_end.record()
+        torch.cuda.synchronize()
+        clocks = sampler.stop()
+        if dist:
+            dist.barrier()
+        ms_total = t_begin.elapsed_time(t_end)
+        if graphs:   # graph replays carry no inner events: time the lookup block in a separate eager pass
+            for i in range(min(args.steps, 20)):
+                step(sets[i % n_sets], (ev_l0[i], ev_l1[i]))
+            torch.cuda.synchronize()
+            n_ev = min(args.steps, 20)
+        else:
+            n_ev = args.steps
+        lookup_ms = sum(ev_l0[i].elapsed_time(ev_l1[i]) for i in range(n_ev)) / (n_ev * ITERS)
+
+        # ---- end-to-end leg: pinned host buffers -> public module API -> pinned host results ----
+        e2e_steps = args.e2e_steps or min(args.steps, 10)
+        host = make_unit(wl, seed=1002 + 17 * rank, pin=True)
+        h_outs = torch.empty(ITERS, P, K81, H, W, dtype=torch.float32).pin_memory()
+        h_warp = torch.empty(P, 1, IH, IW, dtype=torch.float32).pin_memory()
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+        d2h = h_outs.numel() * 4 + h_warp.numel() * 4
+
+        def e2e_step():
+            d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+            b = cf.CorrBlock(d["f1"], d["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                             pyramid_buffer=pyramid)
+            for k in range(ITERS):
+                b(d["coords"][k], out=outs[k])
+                h_outs[k].copy_(outs[k], non_blocking=True)
+            w = st(flow=d["flow"], original=d["img"])
+            h_warp.copy_(w, non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        e1.record()
+        torch.cuda.synchronize()
+        e2e_ms = e0.elapsed_time(e1)
+
+    if dist:
+        t = torch.tensor([ms_total, e2e_ms, lookup_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms, lookup_ms = t.tolist()
+    value = world * P * args.steps / (ms_total * 1e-3)
+    e2e_value = world * P * e2e_steps / (e2e_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (lookup: 12 of the step's launches, ~80 % of its bytes) ----
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as f:
+            peak, peak_src = json.load(f)["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (copy, read+write)"
+    else:
+        peak, peak_src = 6650.0, "fallback from B200_PROFILING.md"
+    lookup_bytes = oracle_meta.lookup_algorithmic_bytes(P, H, W, LEVELS, RADIUS)
+    achieved = lookup_bytes / (lookup_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "lookup_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(args.workload)
+    n_pool = LEVELS - 1 if used_precision == "fp32" else LEVELS - 2
+    launches_per_step = 1 + n_pool + ITERS + 1
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32" if used_precision == "fp32" else "tf32 GEMM / f32 lookup+warp",
+        "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step_per_gpu": P,
+                   "corr_precision": used_precision, "cuda_graph": bool(graphs),
+                   "l2": f"inputs rotate over {n_sets} sets and each step writes "
+                         f"{(pyr_floats * 4 + outs.numel() * 4) / 1e6:.0f} MB (> 126 MB L2)"},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "frame-pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps},
+        "gpu_launches": launches_per_step * args.steps,
+        "roofline": {"kernel": "lookup_kernel<4>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": lookup_bytes, "avg_launch_ms": lookup_ms,
+                     "frac_of_nominal_8000": achieved / 8000.0},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sample = 4 if args.workload == "cfg2" else 1
+        v, cores, reps = cpu_pairs_per_sec(wl, sample)
+        line["cpu_baseline"] = {"value": v, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
+                                "sample": f"{sample} of {P} pairs (per-pair CorrBlock + 12 lookups + warp), "
+                                          f"torch CPU fp32 oracle, best of {reps}"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,96 @@
+"""ctypes binding of libcardioflow.so (include/cardioflow.h).  No fallback: a missing library is an error."""
+import ctypes
+import os
+import re
+
+import torch
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libcardioflow.so")
+HEADER = os.path.join(os.path.dirname(PKG), "include", "cardioflow.h")
+
+CF_OK, CF_ERR_BAD_ARG, CF_ERR_UNSUPPORTED, CF_ERR_CUDA = 0, -1, -2, -3
+PREC_TF32, PREC_FP32, PREC_AUTO = 0, 1, 2
+MODE_BILINEAR, MODE_NEAREST = 0, 1
+PRECISIONS = {"tf32": PREC_TF32, "fp32": PREC_FP32, "auto": PREC_AUTO}
+
+_c = ctypes
+_P, _I, _Z = _c.c_void_p, _c.c_int, _c.c_size_t
+_SIGNATURES = {
+    "cf_version": (_I, []),
+    "cf_last_error": (_c.c_char_p, []),
+    "cf_pyramid_level_dims": (_I, [_I, _I, _I, _c.POINTER(_I), _c.POINTER(_I)]),
+    "cf_corr_pyramid_level_offset": (_Z, [_I, _I, _I, _I]),
+    "cf_corr_pyramid_bytes": (_Z, [_I, _I, _I, _I]),
+    "cf_coords_grid": (_I, [_P, _I, _I, _I, _P]),
+    "cf_corr_build": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _c.POINTER(_I), _P]),
+    "cf_corr_pool": (_I, [_P, _I, _I, _I, _I, _I, _P]),
+    "cf_corr_lookup": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_corr_lookup_taps": (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_fmap_pyramid_level_offset": (_Z, [_I, _I, _I, _I, _I]),
+    "cf_fmap_pyramid_bytes": (_Z, [_I, _I, _I, _I, _I]),
+    "cf_fmap_pyramid_build": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_corr_lookup_fused": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_warp2d": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_warp2d_taps": (_I, [_P, _I, _I, _I, _P, _P]),
+    "cf_warp2d_onehot_argmax": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
+    "cf_warp2d_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_corr_lookup_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_corr_pool_bwd": (_I, [_P, _I, _I, _I, _I, _P]),
+    "cf_corr_volume_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_vecint": (_I, [_P, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_sample_points": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+}
+
+_lib = None
+
+
+def declared_symbols():
+    """Every entry point include/cardioflow.h declares (used by the symbol-export test)."""
+    with open(HEADER) as f:
+        return sorted(set(re.findall(r"^CF_API[^\n(]*?\b(cf_\w+)\(", f.read(), flags=re.M)))
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+                "cardioflow_b200 has no CPU / eager fallback.")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def check(rc, what=""):
+    if rc == CF_OK:
+        return
+    msg = lib().cf_last_error().decode() or f"{what} failed with code {rc}"
+    if rc in (CF_ERR_BAD_ARG, CF_ERR_UNSUPPORTED):
+        raise ValueError(msg)
+    raise RuntimeError(msg)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("cardioflow_b200 runs on CUDA tensors only (there is no CPU fallback; "
+                               "the CPU restatement lives in oracle/ and is test infrastructure)")
+    dev = tensors[0].device
+    for t in tensors[1:]:
+        if t.device != dev:
+            raise ValueError(f"tensors on different devices: {dev} vs {t.device}")
+    return dev
+
+
+def f32c(t):
+    """fp32 contiguous view/copy (RAFT's CorrBlock does .float() on its inputs as well)."""
+    return t.detach().to(torch.float32).contiguous() if (t.dtype != torch.float32 or not t.is_contiguous()) else t.detach()

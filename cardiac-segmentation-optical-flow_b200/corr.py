@@ -1,0 +1,186 @@
+"""CorrBlock / coords_grid with the reference's call-site API, on hand-written sm_100a kernels.
+
+Call-site contract (reference = /root/reference):
+  ``from nnunet.lib.raft_initial import CorrBlock, BasicUpdateBlock, coords_grid``
+      (nnunet/network_architecture/SegFlowGaussian.py:42 -- the file itself was never committed)
+  ``corr_fn = CorrBlock(fmap1, fmap2, radius=4)``   (:929, 1030, 1161, 1270, 1390, ...)
+  ``corr = corr_fn(coords1)``                       (:935; coords [B,2,H/8,W/8], ch0 = x, ch1 = y)
+  ``coords_grid(N, H//8, W//8, device=img.device)`` (:839-840)
+Arithmetic: public RAFT core/corr.py == torchvision models/optical_flow/raft.py:387-431.
+"""
+import os
+
+import torch
+
+from . import _cabi
+
+
+def coords_grid(batch, ht, wd, device="cuda"):
+    """[batch, 2, ht, wd] fp32 pixel grid, channel 0 = x, channel 1 = y (RAFT utils.coords_grid)."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError("cardioflow_b200.coords_grid needs a CUDA device (no CPU fallback)")
+    out = torch.empty(batch, 2, ht, wd, dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        _cabi.check(_cabi.lib().cf_coords_grid(out.data_ptr(), batch, ht, wd, _cabi.stream()), "cf_coords_grid")
+    return out
+
+
+def _level_views(pyramid, B, H, W, L):
+    lib = _cabi.lib()
+    views = []
+    for lvl in range(L):
+        h, w = H >> lvl, W >> lvl
+        off = lib.cf_corr_pyramid_level_offset(B, H, W, lvl) // 4
+        views.append(pyramid[off:off + B * H * W * h * w].view(B * H * W, 1, h, w))
+    return views
+
+
+class _CorrBuild(torch.autograd.Function):
+    """(fmap1, fmap2) -> packed pyramid.  a2 + a3 of SURVEY.md 8(a)."""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None):
+        B, C, H, W = fmap1.shape
+        lib = _cabi.lib()
+        f1, f2 = _cabi.f32c(fmap1), _cabi.f32c(fmap2)
+        nfloats = lib.cf_corr_pyramid_bytes(B, H, W, num_levels) // 4
+        if pyramid is None:
+            pyramid = torch.empty(nfloats, dtype=torch.float32, device=f1.device)
+        elif pyramid.numel() < nfloats or pyramid.dtype != torch.float32 or not pyramid.is_contiguous():
+            raise ValueError(f"pyramid_buffer must be a contiguous fp32 tensor of >= {nfloats} elements")
+        else:
+            pyramid = pyramid.view(-1)[:nfloats]
+        used = _cabi.ctypes.c_int(-1)
+        with torch.cuda.device(f1.device):
+            _cabi.check(lib.cf_corr_build(f1.data_ptr(), f2.data_ptr(), B, C, H, W, num_levels, precision,
+                                          pyramid.data_ptr(), _cabi.ctypes.byref(used), _cabi.stream()), "cf_corr_build")
+        ctx.save_for_backward(f1, f2)
+        ctx.meta = (B, C, H, W, num_levels)
+        ctx.used_precision = used.value
+        _CorrBuild.last_used_precision = used.value
+        return pyramid
+
+    @staticmethod
+    def backward(ctx, grad_pyramid):
+        f1, f2 = ctx.saved_tensors
+        B, C, H, W, L = ctx.meta
+        lib = _cabi.lib()
+        g = grad_pyramid.contiguous().clone()
+        gf1, gf2 = torch.empty_like(f1), torch.empty_like(f2)
+        with torch.cuda.device(f1.device):
+            s = _cabi.stream()
+            _cabi.check(lib.cf_corr_pool_bwd(g.data_ptr(), B, H, W, L, s), "cf_corr_pool_bwd")
+            _cabi.check(lib.cf_corr_volume_bwd(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W,
+                                               gf1.data_ptr(), gf2.data_ptr(), s), "cf_corr_volume_bwd")
+        return gf1, gf2, None, None, None
+
+
+class _CorrLookup(torch.autograd.Function):
+    """(packed pyramid, coords) -> [B, L*(2r+1)^2, H, W].  a4 of SURVEY.md 8(a); no gradient w.r.t. coords
+    (the reference detaches them before every lookup, SegFlowGaussian.py:933)."""
+
+    @staticmethod
+    def forward(ctx, pyramid, coords, meta, out=None):
+        B, H, W, L, r = meta
+        c = _cabi.f32c(coords)
+        shape = (B, L * (2 * r + 1) ** 2, H, W)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float32, device=pyramid.device)
+        elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous fp32 tensor of shape {shape}")
+        with torch.cuda.device(pyramid.device):
+            _cabi.check(_cabi.lib().cf_corr_lookup(pyramid.data_ptr(), c.data_ptr(), B, H, W, L, r, out.data_ptr(),
+                                                   _cabi.stream()), "cf_corr_lookup")
+        ctx.save_for_backward(c)
+        ctx.meta = meta
+        ctx.numel = pyramid.numel()
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (c,) = ctx.saved_tensors
+        B, H, W, L, r = ctx.meta
+        g = torch.zeros(ctx.numel, dtype=torch.float32, device=grad_out.device)
+        go = grad_out.contiguous().float()
+        with torch.cuda.device(go.device):
+            _cabi.check(_cabi.lib().cf_corr_lookup_bwd(c.data_ptr(), go.data_ptr(), B, H, W, L, r, g.data_ptr(),
+                                                       _cabi.stream()), "cf_corr_lookup_bwd")
+        return g, None, None, None
+
+
+class CorrBlock:
+    """Drop-in for RAFT's ``CorrBlock(fmap1, fmap2, num_levels=4, radius=4)``; instances are callable.
+
+    ``precision``: "tf32" (tcgen05 tensor cores), "fp32" (CUDA cores, exact-precision mode) or "auto"
+    (default; env ``CARDIOFLOW_CORR_PRECISION``).  ``pyramid_buffer`` / ``out=`` let a caller that loops over
+    frame pairs reuse device memory (the reference allocates afresh every call).  Errors follow torchvision raft.py:368-383 (ValueError).
+    """
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None, pyramid_buffer=None):
+        if fmap1.shape != fmap2.shape:
+            raise ValueError(f"Input feature maps should have the same shape, instead got {tuple(fmap1.shape)} "
+                             f"(fmap1.shape) != {tuple(fmap2.shape)} (fmap2.shape)")
+        if fmap1.dim() != 4:
+            raise ValueError(f"feature maps must be [B, C, H, W], got {tuple(fmap1.shape)}")
+        min_size = 2 * (2 ** (num_levels - 1))
+        if any(s < min_size for s in fmap1.shape[-2:]):
+            raise ValueError("Feature maps are too small to be down-sampled by the correlation pyramid. "
+                             f"H and W of feature maps should be at least {min_size}; got: {tuple(fmap1.shape[-2:])}.")
+        _cabi.require_cuda(fmap1, fmap2)
+        precision = precision or os.environ.get("CARDIOFLOW_CORR_PRECISION", "auto")
+        if precision not in _cabi.PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_cabi.PRECISIONS)}, got {precision!r}")
+        self.num_levels = num_levels
+        self.radius = radius
+        B, _, H, W = fmap1.shape
+        self._meta = (B, H, W, num_levels, radius)
+        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer)
+        self.used_precision = {0: "tf32", 1: "fp32"}.get(getattr(_CorrBuild, "last_used_precision", -1), "?")
+        self.corr_pyramid = _level_views(self._pyramid, B, H, W, num_levels)
+
+    @classmethod
+    def from_pyramid(cls, levels, radius=4):
+        """Wrap an existing pyramid (list of [B*H*W, 1, h_l, w_l] tensors, level 0 first) -- used by the parity
+        tests to isolate the lookup from the GEMM precision, and by the torchvision adaptor."""
+        self = cls.__new__(cls)
+        lvl0 = levels[0]
+        H, W = lvl0.shape[-2:]
+        B = lvl0.shape[0] // (H * W)
+        L = len(levels)
+        _cabi.require_cuda(*levels)
+        lib = _cabi.lib()
+        packed = torch.zeros(lib.cf_corr_pyramid_bytes(B, H, W, L) // 4, dtype=torch.float32, device=lvl0.device)
+        self.num_levels, self.radius = L, radius
+        self._meta = (B, H, W, L, radius)
+        self._pyramid = packed
+        self.used_precision = "external"
+        self.corr_pyramid = _level_views(packed, B, H, W, L)
+        for view, src in zip(self.corr_pyramid, levels):
+            view.copy_(src.reshape(view.shape))
+        return self
+
+    def __call__(self, coords, out=None):
+        B, H, W, _, _ = self._meta
+        if tuple(coords.shape) != (B, 2, H, W):
+            raise ValueError(f"coords must be [{B}, 2, {H}, {W}], got {tuple(coords.shape)}")
+        _cabi.require_cuda(self._pyramid, coords)
+        return _CorrLookup.apply(self._pyramid, coords, self._meta, out)
+
+    # torchvision-style aliases, so the same object can stand in for raft_large().corr_block's methods
+    index_pyramid = __call__
+
+
+def lookup_taps(coords, num_levels=4, radius=4):
+    """Parity hook: sampling coordinates / floors the lookup kernel derives.  Returns (taps, idx) with shape
+    [L, B*H*W, 2, 2r+1] (axis 2: 0 = x, 1 = y)."""
+    B, _, H, W = coords.shape
+    _cabi.require_cuda(coords)
+    c = _cabi.f32c(coords)
+    side = 2 * radius + 1
+    taps = torch.empty(num_levels, B * H * W, 2, side, dtype=torch.float32, device=c.device)
+    idx = torch.empty(num_levels, B * H * W, 2, side, dtype=torch.int32, device=c.device)
+    with torch.cuda.device(c.device):
+        _cabi.check(_cabi.lib().cf_corr_lookup_taps(c.data_ptr(), B, H, W, num_levels, radius, taps.data_ptr(),
+                                                    idx.data_ptr(), _cabi.stream()), "cf_corr_lookup_taps")
+    return taps, idx

@@ -1,0 +1,171 @@
+// extern "C" entry points of libcardioflow.so (include/cardioflow.h): argument validation + dispatch.
+#include <cmath>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace cf {
+
+char* error_buffer() {
+    static thread_local char buf[512] = "";
+    return buf;
+}
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(error_buffer(), 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+bool corr_level_dims(int B, int H, int W, int L, LevelDims* d) {
+    size_t off = 0;
+    int h = H, w = W;
+    for (int l = 0; l < L; ++l) {
+        if (h < 1 || w < 1) return false;
+        d->h[l] = h;
+        d->w[l] = w;
+        d->off[l] = off;
+        off += round_up((size_t)B * H * W * h * w * sizeof(float), 256);
+        h /= 2;
+        w /= 2;
+    }
+    d->off[L] = off;
+    return true;
+}
+
+namespace {
+int check_corr_shape(int B, int H, int W, int L, LevelDims* d) {
+    CF_REQUIRE(B > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "B, H, W must be positive (got %d, %d, %d)", B, H, W);
+    CF_REQUIRE(L >= 1 && L <= CF_MAX_LEVELS, CF_ERR_UNSUPPORTED, "num_levels %d not in [1,%d]", L, CF_MAX_LEVELS);
+    // torchvision raft.py:368-383: the coarsest level must keep at least 2 values per axis
+    const int min_size = 2 << (L - 1);
+    CF_REQUIRE(H >= min_size && W >= min_size, CF_ERR_UNSUPPORTED,
+               "feature maps %dx%d too small for %d pyramid levels (need >= %d)", H, W, L, min_size);
+    CF_REQUIRE(corr_level_dims(B, H, W, L, d), CF_ERR_UNSUPPORTED, "empty pyramid level");
+    return CF_OK;
+}
+}  // namespace
+
+}  // namespace cf
+
+using namespace cf;
+
+extern "C" {
+
+int cf_version(void) { return 100; }
+
+const char* cf_last_error(void) { return error_buffer(); }
+
+int cf_pyramid_level_dims(int H, int W, int level, int* h_out, int* w_out) {
+    CF_REQUIRE(level >= 0 && level < CF_MAX_LEVELS && h_out && w_out, CF_ERR_BAD_ARG, "bad level %d", level);
+    *h_out = H >> level;
+    *w_out = W >> level;
+    return CF_OK;
+}
+
+size_t cf_corr_pyramid_level_offset(int B, int H, int W, int level) {
+    LevelDims d;
+    if (level < 0 || level > CF_MAX_LEVELS || !corr_level_dims(B, H, W, level, &d)) return 0;
+    return d.off[level];
+}
+
+size_t cf_corr_pyramid_bytes(int B, int H, int W, int L) { return cf_corr_pyramid_level_offset(B, H, W, L); }
+
+int cf_coords_grid(float* out, int B, int H, int W, void* stream) {
+    CF_REQUIRE(out && B > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_coords_grid: bad argument");
+    return launch_coords_grid(out, B, H, W, (cudaStream_t)stream);
+}
+
+int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
+                  float* pyramid, int* used_precision, void* stream) {
+    CF_REQUIRE(f1 && f2 && pyramid, CF_ERR_BAD_ARG, "cf_corr_build: null pointer");
+    CF_REQUIRE(C > 0, CF_ERR_BAD_ARG, "cf_corr_build: C must be positive");
+    CF_REQUIRE(((uintptr_t)pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_build: pyramid must be 256-byte aligned");
+    CF_REQUIRE(precision == CF_PREC_TF32 || precision == CF_PREC_FP32 || precision == CF_PREC_AUTO, CF_ERR_BAD_ARG,
+               "cf_corr_build: unknown precision %d", precision);
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    float* level0 = pyramid;
+    float* level1 = L > 1 ? reinterpret_cast<float*>(reinterpret_cast<char*>(pyramid) + d.off[1]) : nullptr;
+
+    int from_level = 0;
+    int used = CF_PREC_FP32;
+    if (precision != CF_PREC_FP32) {
+        const bool fuse = level1 && corr_tcgen05_supported(B, C, H, W, true) && aligned16(f1) && aligned16(f2);
+        const bool plain = !fuse && corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2);
+        if (fuse || plain) {
+            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, level0, fuse ? level1 : nullptr, s);
+            if (rc) return rc;
+            used = CF_PREC_TF32;
+            from_level = fuse ? 1 : 0;
+        } else if (precision == CF_PREC_TF32) {
+            return fail(CF_ERR_UNSUPPORTED,
+                        "cf_corr_build: shape B=%d C=%d H=%d W=%d does not fit the tcgen05 tiling "
+                        "(need H*W %% 4 == 0, C %% 8 == 0, 16-byte aligned inputs); use CF_PREC_AUTO or CF_PREC_FP32",
+                        B, C, H, W);
+        }
+    }
+    if (used == CF_PREC_FP32) {
+        rc = launch_corr_simt(f1, f2, B, C, H * W, level0, s);
+        if (rc) return rc;
+    }
+    if (used_precision) *used_precision = used;
+    return launch_pool_chain(pyramid, d, (long)B * H * W, L, from_level, s);
+}
+
+int cf_corr_pool(float* pyramid, int B, int H, int W, int L, int from_level, void* stream) {
+    CF_REQUIRE(pyramid, CF_ERR_BAD_ARG, "cf_corr_pool: null pointer");
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    CF_REQUIRE(from_level >= 0 && from_level < L, CF_ERR_BAD_ARG, "cf_corr_pool: from_level %d not in [0,%d)", from_level, L);
+    return launch_pool_chain(pyramid, d, (long)B * H * W, L, from_level, (cudaStream_t)stream);
+}
+
+int cf_corr_lookup(const float* pyramid, const float* coords, int B, int H, int W, int L, int r, float* out,
+                   void* stream) {
+    CF_REQUIRE(pyramid && coords && out, CF_ERR_BAD_ARG, "cf_corr_lookup: null pointer");
+    CF_REQUIRE(r >= 1 && r <= CF_MAX_RADIUS, CF_ERR_UNSUPPORTED, "cf_corr_lookup: radius %d not in [1,%d]", r, CF_MAX_RADIUS);
+    CF_REQUIRE(((uintptr_t)pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_lookup: pyramid must be 256-byte aligned");
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    return launch_lookup(pyramid, d, coords, B, H, W, L, r, out, (cudaStream_t)stream);
+}
+
+int cf_corr_lookup_taps(const float* coords, int B, int H, int W, int L, int r, float* taps, int32_t* idx,
+                        void* stream) {
+    CF_REQUIRE(coords && taps && idx, CF_ERR_BAD_ARG, "cf_corr_lookup_taps: null pointer");
+    CF_REQUIRE(r >= 1 && r <= CF_MAX_RADIUS, CF_ERR_UNSUPPORTED, "cf_corr_lookup_taps: radius %d not in [1,%d]", r, CF_MAX_RADIUS);
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    return launch_lookup_taps(d, coords, B, H, W, L, r, taps, idx, (cudaStream_t)stream);
+}
+
+int cf_warp2d(const float* flow, const float* src, int B, int C, int H, int W, int mode, float* out, void* stream) {
+    CF_REQUIRE(flow && src && out, CF_ERR_BAD_ARG, "cf_warp2d: null pointer");
+    CF_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_warp2d: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    CF_REQUIRE(mode == CF_MODE_BILINEAR || mode == CF_MODE_NEAREST, CF_ERR_UNSUPPORTED, "cf_warp2d: mode %d", mode);
+    CF_REQUIRE(out != src && out != flow, CF_ERR_BAD_ARG, "cf_warp2d: out must not alias the inputs");
+    return launch_warp2d(flow, src, B, C, H, W, mode, out, (cudaStream_t)stream);
+}
+
+int cf_warp2d_taps(const float* flow, int B, int H, int W, float* taps, void* stream) {
+    CF_REQUIRE(flow && taps && B > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_warp2d_taps: bad argument");
+    return launch_warp2d_taps(flow, B, H, W, taps, (cudaStream_t)stream);
+}
+
+int cf_warp2d_onehot_argmax(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
+                            int64_t* out, void* stream) {
+    CF_REQUIRE(flow && label && out, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax: null pointer");
+    CF_REQUIRE(B > 0 && H > 1 && W > 1 && num_classes > 0, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax: bad shape");
+    CF_REQUIRE(out != label, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax: out must not alias label");
+    return launch_warp2d_onehot_argmax(flow, label, num_classes, B, H, W, out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,100 @@
+// Shared helpers for libcardioflow.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "cardioflow.h"
+
+namespace cf {
+
+// thread-local error message behind cf_last_error()
+char* error_buffer();
+int fail(int code, const char* fmt, ...);
+
+#define CF_CHECK_CUDA(expr)                                                                        \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            return cf::fail(CF_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),   \
+                            __FILE__, __LINE__);                                                   \
+    } while (0)
+
+#define CF_CHECK_LAUNCH(name)                                                                      \
+    do {                                                                                           \
+        cudaError_t _e = cudaGetLastError();                                                       \
+        if (_e != cudaSuccess)                                                                     \
+            return cf::fail(CF_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(_e)); \
+    } while (0)
+
+#define CF_REQUIRE(cond, code, ...)                      \
+    do {                                                 \
+        if (!(cond)) return cf::fail(code, __VA_ARGS__); \
+    } while (0)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+inline size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+inline int cdiv(long a, long b) { return static_cast<int>((a + b - 1) / b); }
+
+struct LevelDims {
+    int h[CF_MAX_LEVELS];
+    int w[CF_MAX_LEVELS];
+    size_t off[CF_MAX_LEVELS + 1];  // byte offsets of the packed corr pyramid, off[L] = total
+};
+// Fills dims for L levels of a [B*H*W, 1, h_l, w_l] pyramid; returns false if a level would be empty.
+bool corr_level_dims(int B, int H, int W, int L, LevelDims* d);
+
+// ---- the exact fp32 coordinate sequences (no FMA contraction: *_rn intrinsics are never fused) ----
+// lookup: RAFT bilinear_sampler n = 2*p/(S-1) - 1, then ATen unnormalize ((n+1)/2)*(S-1)
+__device__ __forceinline__ float lookup_coord(float p, float s1) {
+    const float n = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, p), s1), 1.0f);
+    return __fmul_rn(__fmul_rn(__fadd_rn(n, 1.0f), 0.5f), s1);
+}
+// warp: integration.py:68 n = 2*(p/(S-1) - 0.5), then the same ATen step
+__device__ __forceinline__ float warp_coord(float p, float s1) {
+    const float n = __fmul_rn(2.0f, __fsub_rn(__fdiv_rn(p, s1), 0.5f));
+    return __fmul_rn(__fmul_rn(__fadd_rn(n, 1.0f), 0.5f), s1);
+}
+
+__device__ __forceinline__ float4 ldg_f4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+}  // namespace cf
+
+// kernels' host launchers (one per .cu file)
+namespace cf {
+int launch_coords_grid(float* out, int B, int H, int W, cudaStream_t s);
+int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int W, int mode, float* out,
+                  cudaStream_t s);
+int launch_warp2d_taps(const float* flow, int B, int H, int W, float* taps, cudaStream_t s);
+int launch_warp2d_onehot_argmax(const float* flow, const int64_t* label, int ncls, int B, int H, int W,
+                                int64_t* out, cudaStream_t s);
+int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W,
+                      float* gsrc, float* gflow, cudaStream_t s);
+int launch_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, cudaStream_t s);
+int launch_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int mode,
+                         float* out, cudaStream_t s);
+
+int launch_pool_chain(float* pyramid, const LevelDims& d, long n_img, int L, int from_level, cudaStream_t s);
+int launch_pool_chain_bwd(float* gpyr, const LevelDims& d, long n_img, int L, cudaStream_t s);
+
+int launch_corr_simt(const float* f1, const float* f2, int B, int C, int HW, float* level0, cudaStream_t s);
+// returns CF_ERR_UNSUPPORTED (without touching the stream) when the shape does not fit the TMA/UMMA tiling
+int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* level0,
+                        float* level1 /* may be null: no fused pooling */, cudaStream_t s);
+bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool);
+int launch_corr_volume_bwd(const float* f1, const float* f2, const float* gcorr, int B, int C, int HW,
+                           float* gf1, float* gf2, cudaStream_t s);
+
+int launch_lookup(const float* pyramid, const LevelDims& d, const float* coords, int B, int H, int W, int L,
+                  int r, float* out, cudaStream_t s);
+int launch_lookup_taps(const LevelDims& d, const float* coords, int B, int H, int W, int L, int r, float* taps,
+                       int32_t* idx, cudaStream_t s);
+int launch_lookup_bwd(const LevelDims& d, const float* coords, const float* go, int B, int H, int W, int L,
+                      int r, float* gpyr, cudaStream_t s);
+
+int launch_fmap_pyramid(const float* f2, int B, int C, int H, int W, int L, float* f2pyr, cudaStream_t s);
+int launch_lookup_fused(const float* f1, const float* f2pyr, const float* coords, int B, int C, int H, int W,
+                        int L, int r, float* out, cudaStream_t s);
+}  // namespace cf

@@ -1,0 +1,168 @@
+"""SpatialTransformer / SpatialTransformerContour / VecInt with the reference's module API, on sm_100a kernels.
+
+Mirrors /root/reference/nnunet/network_architecture/integration.py (:37-79, :5-34, :82-99) including its
+quirks: ``forward(flow, original, mode=...)`` with flow first; forward's ``mode`` ignored
+(constructor's used); flow channel 0 displaces rows and channel 1 columns; a float32 ``grid`` buffer
+[1,2,H,W] in the state dict (checkpoints are loaded strictly, network_trainer.py:444).
+"""
+import torch
+import torch.nn as nn
+
+from . import _cabi
+
+_MODES = {"bilinear": _cabi.MODE_BILINEAR, "nearest": _cabi.MODE_NEAREST}
+
+
+class _Warp2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, flow, original, mode, out=None):
+        f, src = _cabi.f32c(flow), _cabi.f32c(original)
+        B, C, H, W = src.shape
+        if out is None:
+            out = torch.empty_like(src)
+        elif out.shape != src.shape or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous fp32 tensor of shape {tuple(src.shape)}")
+        with torch.cuda.device(src.device):
+            _cabi.check(_cabi.lib().cf_warp2d(f.data_ptr(), src.data_ptr(), B, C, H, W, mode, out.data_ptr(),
+                                              _cabi.stream()), "cf_warp2d")
+        ctx.save_for_backward(f, src)
+        ctx.mode = mode
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        f, src = ctx.saved_tensors
+        if ctx.mode != _cabi.MODE_BILINEAR:
+            raise NotImplementedError("backward of the nearest-mode warp is zero almost everywhere; not provided")
+        B, C, H, W = src.shape
+        go = grad_out.contiguous().float()
+        need_flow, need_src = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gsrc = torch.zeros_like(src) if need_src else None
+        gflow = torch.empty_like(f) if need_flow else None
+        with torch.cuda.device(src.device):
+            _cabi.check(_cabi.lib().cf_warp2d_bwd(f.data_ptr(), src.data_ptr(), go.data_ptr(), B, C, H, W,
+                                                  gsrc.data_ptr() if need_src else None,
+                                                  gflow.data_ptr() if need_flow else None, _cabi.stream()),
+                        "cf_warp2d_bwd")
+        return gflow, gsrc, None, None
+
+
+def _check_pair(flow, original, size=None):
+    if flow.dim() != 4 or flow.shape[1] != 2:
+        raise ValueError(f"flow must be [B, 2, H, W], got {tuple(flow.shape)}")
+    if original.dim() != 4 or original.shape[0] != flow.shape[0] or original.shape[2:] != flow.shape[2:]:
+        raise ValueError(f"original must be [B, C, H, W] matching flow {tuple(flow.shape)}, got {tuple(original.shape)}")
+    if size is not None and tuple(flow.shape[2:]) != tuple(size):
+        raise ValueError(f"flow spatial size {tuple(flow.shape[2:])} != transformer size {tuple(size)}")
+    _cabi.require_cuda(flow, original)
+
+
+def warp(src, flow, mode="bilinear", out=None):
+    """Functional alias in voxelmorph's (src, flow) order; the module below keeps the reference's order."""
+    _check_pair(flow, src)
+    return _Warp2d.apply(flow, src, _MODES[mode], out)
+
+
+def warp_onehot_argmax(flow, label, num_classes=4):
+    """argmax_c warp(one_hot(label), flow) without the one-hot intermediate (the `warp_linear` pattern,
+    SegFlowGaussian.py:3571-3580).  label [B,1,H,W] integer; returns int64 [B,1,H,W]."""
+    if label.dim() != 4 or label.shape[1] != 1 or label.shape[0] != flow.shape[0] or label.shape[2:] != flow.shape[2:]:
+        raise ValueError(f"label must be [B, 1, H, W] matching flow {tuple(flow.shape)}, got {tuple(label.shape)}")
+    _cabi.require_cuda(flow, label)
+    f = _cabi.f32c(flow)
+    lab = label.detach().to(torch.int64).contiguous()
+    B, _, H, W = lab.shape
+    out = torch.empty_like(lab)
+    with torch.cuda.device(f.device):
+        _cabi.check(_cabi.lib().cf_warp2d_onehot_argmax(f.data_ptr(), lab.data_ptr(), num_classes, B, H, W,
+                                                        out.data_ptr(), _cabi.stream()), "cf_warp2d_onehot_argmax")
+    return out
+
+
+def warp_taps(flow):
+    """Parity hook: [B,2,H,W] sampling coordinates (ch0 = row, ch1 = column) the warp kernel derives."""
+    _cabi.require_cuda(flow)
+    f = _cabi.f32c(flow)
+    B, _, H, W = f.shape
+    taps = torch.empty_like(f)
+    with torch.cuda.device(f.device):
+        _cabi.check(_cabi.lib().cf_warp2d_taps(f.data_ptr(), B, H, W, taps.data_ptr(), _cabi.stream()), "cf_warp2d_taps")
+    return taps
+
+
+class SpatialTransformer(nn.Module):
+    """N-D spatial transformer of the reference, 2-D only (no caller in the reference builds a 3-D one)."""
+
+    def __init__(self, size, mode="bilinear"):
+        super().__init__()
+        size = tuple(int(s) for s in size)
+        if len(size) != 2:
+            raise ValueError("only the 2-D SpatialTransformer is on the hot path (no 3-D caller exists in the reference)")
+        if mode not in _MODES:
+            raise ValueError(f"mode must be 'bilinear' or 'nearest', got {mode!r}")
+        self.mode = mode
+        self.size = size
+        ys, xs = torch.meshgrid(torch.arange(0, size[0]), torch.arange(0, size[1]), indexing="ij")
+        # kept only for state-dict compatibility (integration.py:59); the kernel derives the grid from indices
+        self.register_buffer("grid", torch.stack([ys, xs]).unsqueeze(0).float())
+
+    def forward(self, flow, original, mode="bilinear"):
+        _check_pair(flow, original, self.size)
+        return _Warp2d.apply(flow, original, _MODES[self.mode])
+
+
+class SpatialTransformerContour(nn.Module):
+    """Samples ``original`` at P points; ``new_locs`` [B,2,1,P] (ch0 = x, ch1 = y, reversed-size
+    normalisation as integration.py:23-24).  Like the reference it normalises ``new_locs`` IN PLACE."""
+
+    def __init__(self, size, mode="bilinear"):
+        super().__init__()
+        if mode not in _MODES:
+            raise ValueError(f"mode must be 'bilinear' or 'nearest', got {mode!r}")
+        self.mode = mode
+        self.shape = tuple(int(s) for s in size)
+
+    def forward(self, new_locs, original, mode="bilinear"):
+        if new_locs.dim() != 4 or new_locs.shape[1] != 2:
+            raise ValueError(f"new_locs must be [B, 2, h, P], got {tuple(new_locs.shape)}")
+        _cabi.require_cuda(new_locs, original)
+        B, C, H, W = original.shape
+        locs = _cabi.f32c(new_locs)
+        src = _cabi.f32c(original)
+        P = locs.shape[2] * locs.shape[3]
+        out = torch.empty(B, C, locs.shape[2], locs.shape[3], dtype=torch.float32, device=src.device)
+        with torch.cuda.device(src.device):
+            _cabi.check(_cabi.lib().cf_sample_points(locs.data_ptr(), src.data_ptr(), B, C, H, W, P,
+                                                     _MODES[self.mode], out.data_ptr(), _cabi.stream()),
+                        "cf_sample_points")
+        # reference side effect (integration.py:23-24): the argument ends up normalised to [-1, 1]
+        with torch.no_grad():
+            for i in range(2):
+                new_locs[:, i, ...] = 2 * (new_locs[:, i, ...] / (self.shape[~i] - 1) - 0.5)
+        return out
+
+
+class VecInt(nn.Module):
+    """Scaling and squaring (integration.py:82-99): vec / 2^n, then n times vec += warp(vec, vec)."""
+
+    def __init__(self, inshape, nsteps):
+        super().__init__()
+        assert nsteps >= 0, "nsteps should be >= 0, found: %d" % nsteps
+        self.nsteps = nsteps
+        self.scale = 1.0 / (2 ** self.nsteps)
+        self.transformer = SpatialTransformer(inshape)
+
+    def forward(self, vec):
+        if vec.requires_grad and torch.is_grad_enabled():
+            vec = vec * self.scale  # autograd path: compose from the differentiable warp
+            for _ in range(self.nsteps):
+                vec = vec + self.transformer(vec, vec)
+            return vec
+        _check_pair(vec, vec, self.transformer.size)
+        v = _cabi.f32c(vec)
+        B, _, H, W = v.shape
+        out, work = torch.empty_like(v), torch.empty_like(v)
+        with torch.cuda.device(v.device):
+            _cabi.check(_cabi.lib().cf_vecint(v.data_ptr(), B, H, W, self.nsteps, out.data_ptr(), work.data_ptr(),
+                                              _cabi.stream()), "cf_vecint")
+        return out

@@ -1,0 +1,138 @@
+/* cardioflow.h -- C ABI of libcardioflow.so: the B200 (sm_100a) optical-flow hot path.
+ *
+ * This is the drop-in boundary for ONE path of nicolas1805961/Cardiac-Segmentation-Optical-flow: the RAFT
+ * correlation block (all-pairs correlation -> avg-pooled pyramid -> radius-r bilinear lookup) and the
+ * voxelmorph-style dense warp.  The reference has no FFI of its own (it is pure Python on torch); each entry
+ * point below names the reference interface it replaces.  Python host code binds these with ctypes
+ * (cardiac-segmentation-optical-flow_b200/_cabi.py); INTEGRATION.md shows the reference-side stub.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into caller-owned memory (torch storage); the library never
+ *     allocates or frees caller-visible memory;
+ *   - all tensors are dense row-major ("contiguous NCHW"), float32 unless said otherwise;
+ *   - `stream` is a cudaStream_t cast to void*; every call only ENQUEUES work on it (no host sync);
+ *   - return value: 0 = ok, CF_ERR_* < 0 otherwise; cf_last_error() gives a thread-local message;
+ *   - there is no CPU fallback: without a CUDA device every compute entry point returns CF_ERR_CUDA.
+ */
+#ifndef CARDIOFLOW_H_
+#define CARDIOFLOW_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CF_API __attribute__((visibility("default")))
+#else
+#define CF_API
+#endif
+
+#define CF_OK 0
+#define CF_ERR_BAD_ARG (-1)     /* null pointer, non-positive size, misaligned pointer            */
+#define CF_ERR_UNSUPPORTED (-2) /* shape / radius / level count outside what the kernels implement */
+#define CF_ERR_CUDA (-3)        /* CUDA runtime / driver error (message in cf_last_error)          */
+
+#define CF_MAX_LEVELS 8
+#define CF_MAX_RADIUS 4
+
+/* cf_corr_build precision */
+#define CF_PREC_TF32 0 /* tcgen05.mma kind::tf32 on the raw fp32 feature maps, fp32 accumulate in TMEM */
+#define CF_PREC_FP32 1 /* CUDA-core fp32 FMA (exact-precision mode; also serves shapes the TMA path rejects) */
+#define CF_PREC_AUTO 2 /* TF32 tensor-core path when the shape allows it, FP32 otherwise                */
+
+/* cf_warp2d interpolation */
+#define CF_MODE_BILINEAR 0
+#define CF_MODE_NEAREST 1
+
+CF_API int cf_version(void);
+CF_API const char* cf_last_error(void);
+
+/* ---- pyramid geometry -------------------------------------------------------------------------------
+ * The pyramid of one CorrBlock is ONE packed buffer.  Level l is the dense tensor [B*H*W, 1, h_l, w_l]
+ * (exactly torchvision's / RAFT's corr_pyramid[l] layout) with h_l = floor(h_{l-1} / 2); level offsets
+ * are rounded up to 256 bytes.  (reference: raft.py:385-392 `corr_pyramid`) */
+CF_API int cf_pyramid_level_dims(int H, int W, int level, int* h_out, int* w_out);
+CF_API size_t cf_corr_pyramid_level_offset(int B, int H, int W, int level); /* byte offset of level `level` */
+CF_API size_t cf_corr_pyramid_bytes(int B, int H, int W, int L);            /* bytes for levels 0..L-1      */
+
+/* ---- a1: coords_grid(batch, ht, wd, device) ------------------------------------------------------------
+ * replaces `coords_grid` imported at nnunet/network_architecture/SegFlowGaussian.py:42, used :839-840
+ * (torchvision twin: _utils.py:22-26).  out [B,2,H,W]: channel 0 = x (column), channel 1 = y (row). */
+CF_API int cf_coords_grid(float* out, int B, int H, int W, void* stream);
+
+/* ---- a2 + a3: CorrBlock.__init__ -------------------------------------------------------------------------
+ * replaces `CorrBlock(fmap1, fmap2, radius=4)` (SegFlowGaussian.py:929 and 9 more call sites) =
+ * torchvision raft.py:424-431 (`matmul(f1^T, f2) / sqrt(C)`) + raft.py:387-392 (3x avg_pool2d).
+ * f1, f2 [B,C,H,W] fp32.  Writes all L levels into `pyramid` (cf_corr_pyramid_bytes).
+ * `used_precision` (optional) receives the precision actually used (CF_PREC_TF32 / CF_PREC_FP32). */
+CF_API int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
+                  float* pyramid, int* used_precision, void* stream);
+
+/* Rebuild levels from_level+1 .. L-1 from level from_level (F.avg_pool2d(x, 2, stride=2), floor mode). */
+CF_API int cf_corr_pool(float* pyramid, int B, int H, int W, int L, int from_level, void* stream);
+
+/* ---- a4: CorrBlock.__call__(coords) ------------------------------------------------------------------------
+ * replaces `corr_fn(coords1)` (SegFlowGaussian.py:935, 12x per frame pair) = torchvision raft.py:394-422.
+ * coords [B,2,H,W] absolute pixel coordinates (ch0 = x, ch1 = y); out [B, L*(2r+1)^2, H, W];
+ * channel l*(2r+1)^2 + i*(2r+1) + j samples level l at (x/2^l + i - r, y/2^l + j - r), bilinear,
+ * align_corners=True, zero padding.  1 <= r <= CF_MAX_RADIUS. */
+CF_API int cf_corr_lookup(const float* pyramid, const float* coords, int B, int H, int W, int L, int r, float* out,
+                   void* stream);
+
+/* Parity hook: the fp32 sampling coordinates the lookup kernel derives (after the normalise ->
+ * un-normalise round trip) and their floors.  taps float[L][B*H*W][2][2r+1] (axis 2: 0 = x, 1 = y),
+ * idx int32 same shape.  Same device code as cf_corr_lookup. */
+CF_API int cf_corr_lookup_taps(const float* coords, int B, int H, int W, int L, int r, float* taps, int32_t* idx,
+                        void* stream);
+
+/* On-the-fly variant (optional path of north_star): lookup without a materialised volume.  f2_pyramid holds
+ * fmap2 average-pooled L-1 times, packed like [B,C,h_l,w_l] per level at cf_fmap_pyramid_level_offset.
+ * Uses linearity: avg_pool over q of <f1[p], f2[q]> == <f1[p], avg_pool(f2)[q]>. */
+CF_API size_t cf_fmap_pyramid_level_offset(int B, int C, int H, int W, int level);
+CF_API size_t cf_fmap_pyramid_bytes(int B, int C, int H, int W, int L);
+CF_API int cf_fmap_pyramid_build(const float* f2, int B, int C, int H, int W, int L, float* f2_pyramid, void* stream);
+CF_API int cf_corr_lookup_fused(const float* f1, const float* f2_pyramid, const float* coords, int B, int C, int H,
+                         int W, int L, int r, float* out, void* stream);
+
+/* ---- a5: SpatialTransformer.forward(flow, original) ----------------------------------------------------------
+ * replaces nnunet/network_architecture/integration.py:61-79.  flow [B,2,H,W] (ch0 displaces rows, ch1
+ * displaces columns), src [B,C,H,W], out [B,C,H,W]; align_corners=True, zero padding. */
+CF_API int cf_warp2d(const float* flow, const float* src, int B, int C, int H, int W, int mode, float* out,
+              void* stream);
+
+/* Parity hook: sampling coordinates of the warp, taps [B,2,H,W] (ch0 = row coordinate, ch1 = column). */
+CF_API int cf_warp2d_taps(const float* flow, int B, int H, int W, float* taps, void* stream);
+
+/* ---- a6: one_hot -> warp -> argmax ------------------------------------------------------------------------------
+ * replaces the `warp_linear` pattern, SegFlowGaussian.py:3571-3580 (and trainer :2430-2457).
+ * label int64 [B,1,H,W] with values in [0, num_classes); out int64 [B,1,H,W]. */
+CF_API int cf_warp2d_onehot_argmax(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
+                            int64_t* out, void* stream);
+
+/* ---- 8(f) next rows ---------------------------------------------------------------------------------------------
+ * Backward passes (autograd): gradients of the warp w.r.t. src and flow, of the lookup w.r.t. the pyramid,
+ * of the pooling chain and of the correlation w.r.t. both feature maps.  grad_* outputs that accumulate
+ * (atomics) must be zero-initialised by the caller. */
+CF_API int cf_warp2d_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W,
+                  float* grad_src /* zeroed, may be NULL */, float* grad_flow /* may be NULL */, void* stream);
+CF_API int cf_corr_lookup_bwd(const float* coords, const float* grad_out, int B, int H, int W, int L, int r,
+                       float* grad_pyramid /* zeroed, packed like the pyramid */, void* stream);
+CF_API int cf_corr_pool_bwd(float* grad_pyramid, int B, int H, int W, int L, void* stream);
+CF_API int cf_corr_volume_bwd(const float* f1, const float* f2, const float* grad_corr /* level 0 */, int B, int C,
+                       int H, int W, float* grad_f1, float* grad_f2, void* stream);
+
+/* VecInt (integration.py:82-99): vec/2^n then n x (vec += warp(vec, vec)); work = scratch [B,2,H,W]. */
+CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream);
+
+/* SpatialTransformerContour (integration.py:5-34): sample src [B,C,H,W] at P points; locs [B,2,P] with
+ * ch0 = x, ch1 = y (the reference's un-swapped order); out [B,C,P]. */
+CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int mode,
+                     float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CARDIOFLOW_H_ */

@@ -1,0 +1,88 @@
+"""CPU: the C-ABI library loads, exports what include/cardioflow.h declares, and the host mirror of the
+reference's module API validates arguments / keeps the state-dict contract.  No compute calls here."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import cardioflow_b200 as cf
+from cardioflow_b200 import _cabi
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    lib = _cabi.lib()
+    declared = _cabi.declared_symbols()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/cardioflow.h but not exported"
+        assert name in _cabi._SIGNATURES, f"{name} has no ctypes signature"
+    assert lib.cf_version() >= 100
+
+
+def test_pyramid_geometry():
+    lib = _cabi.lib()
+    B, H, W, L = 2, 24, 24, 4
+    sizes = [24, 12, 6, 3]
+    off = 0
+    for lvl, s in enumerate(sizes):
+        assert lib.cf_corr_pyramid_level_offset(B, H, W, lvl) == off
+        off += -(-(B * H * W * s * s * 4) // 256) * 256
+        h, w = ctypes.c_int(), ctypes.c_int()
+        assert lib.cf_pyramid_level_dims(H, W, lvl, ctypes.byref(h), ctypes.byref(w)) == 0
+        assert (h.value, w.value) == (s, s)
+    assert lib.cf_corr_pyramid_bytes(B, H, W, L) == off
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    lib = _cabi.lib()
+    assert lib.cf_corr_lookup(None, None, 1, 16, 16, 4, 4, None, None) == _cabi.CF_ERR_BAD_ARG
+    assert b"null" in lib.cf_last_error()
+    assert lib.cf_corr_lookup_taps(ctypes.c_void_p(256), 1, 8, 8, 4, 4, ctypes.c_void_p(256), ctypes.c_void_p(256), None) \
+        == _cabi.CF_ERR_UNSUPPORTED                      # 8x8 too small for 4 levels (raft.py:368-383)
+    assert lib.cf_corr_lookup_taps(ctypes.c_void_p(256), 1, 16, 16, 4, 5, ctypes.c_void_p(256), ctypes.c_void_p(256), None) \
+        == _cabi.CF_ERR_UNSUPPORTED                      # radius > CF_MAX_RADIUS
+
+
+def test_no_cpu_fallback():
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        cf.CorrBlock(torch.randn(1, 8, 16, 16), torch.randn(1, 8, 16, 16))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        cf.SpatialTransformer((8, 8))(torch.zeros(1, 2, 8, 8), torch.zeros(1, 1, 8, 8))
+    with pytest.raises(RuntimeError):
+        cf.coords_grid(1, 4, 4, device="cpu")
+
+
+def test_corrblock_validation_matches_torchvision_errors():
+    with pytest.raises(ValueError, match="same shape"):
+        cf.CorrBlock(torch.randn(1, 8, 16, 16), torch.randn(1, 8, 16, 24))
+    with pytest.raises(ValueError, match="too small"):
+        cf.CorrBlock(torch.randn(1, 8, 8, 8), torch.randn(1, 8, 8, 8))
+
+
+def test_spatial_transformer_module_contract(golden_warp):
+    st = cf.SpatialTransformer((6, 5))
+    sd = st.state_dict()
+    assert list(sd.keys()) == ["grid"] and sd["grid"].dtype == torch.float32
+    assert np.array_equal(sd["grid"].numpy(), golden_warp["state.grid_6x5"])
+    # strict load of a state dict produced by the REFERENCE module (frozen in the fixture)
+    st.load_state_dict({"grid": torch.from_numpy(golden_warp["state.grid_6x5"])}, strict=True)
+    import inspect
+    assert list(inspect.signature(st.forward).parameters) == ["flow", "original", "mode"]
+    with pytest.raises(ValueError):
+        cf.SpatialTransformer((4, 4, 4))
+    v = cf.VecInt((8, 8), 3)
+    assert list(v.state_dict().keys()) == ["transformer.grid"] and v.scale == 0.125
+
+
+def test_shim_modules_resolve_to_this_package():
+    import importlib.util, os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for rel, names in (("shim/nnunet/lib/raft_initial.py", ["CorrBlock", "coords_grid"]),
+                       ("shim/nnunet/network_architecture/integration.py",
+                        ["SpatialTransformer", "SpatialTransformerContour", "VecInt"])):
+        spec = importlib.util.spec_from_file_location("shim_" + os.path.basename(rel)[:-3], os.path.join(root, rel))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        for n in names:
+            assert getattr(mod, n) is getattr(cf, n)

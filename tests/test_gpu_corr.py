@@ -1,0 +1,192 @@
+"""GPU parity: CorrBlock (pyramid build + lookup) through the C ABI / module API against the oracle.
+
+Tolerances (BASELINE.json north_star): tap indices / coordinates bit-exact; fp32 lookup <= 1e-5 relative
+(max|diff| / max|ref|) -- and bit-exact against the C oracle on the same pyramid; pooling bit-exact; fp32
+correlation <= 1e-5 relative (summation order); tensor-core (TF32 in, fp32 accumulate) correlation <= 1e-2.
+"""
+import numpy as np
+import pytest
+import torch
+
+import cardioflow_b200 as cf
+from conftest import CORR_CASES, rel_err
+from oracle import c_oracle, corr_oracle, taps
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _gpu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def _coord_sets(g, b, h, w):
+    grid = corr_oracle.coords_grid(b, h, w)
+    border = grid.clone()
+    border[:, 0] = torch.where(grid[:, 0] < w / 2, -0.5, w - 0.5)
+    return {
+        "grid": grid,                                                       # iteration 0: exact integers
+        "noise": grid + torch.randn(b, 2, h, w, generator=g) * 2.0,
+        "border": border,
+        "wide": grid + torch.randn(b, 2, h, w, generator=g) * (w / 2),      # many taps leave the image
+        "far": grid + 1000.0,
+        "negfar": grid - 3000.0,
+    }
+
+
+@pytest.mark.parametrize("name", CORR_CASES)
+def test_golden_fixture(golden_corr, name):
+    f1, f2 = golden_corr[f"{name}.f1"], golden_corr[f"{name}.f2"]
+    blk = cf.CorrBlock(_gpu(f1), _gpu(f2), radius=4, precision="fp32")
+    assert blk.used_precision == "fp32"
+    ref_l0 = corr_oracle.CorrBlock(torch.from_numpy(f1), torch.from_numpy(f2)).corr_pyramid[0].numpy()
+    assert rel_err(blk.corr_pyramid[0].cpu().numpy(), ref_l0) <= 1e-5
+    for lvl in (1, 2, 3):
+        got = blk.corr_pyramid[lvl].cpu().numpy()
+        assert got.shape == golden_corr[f"{name}.pyr{lvl}"].shape
+        assert rel_err(got, golden_corr[f"{name}.pyr{lvl}"]) <= 1e-5
+        # pooling itself is bit-exact: level l+1 == ATen-order pooling of OUR level l
+        assert np.array_equal(got[:, 0], taps.avg_pool2x2(blk.corr_pyramid[lvl - 1].cpu().numpy()[:, 0]))
+    for k in range(4):
+        out = blk(_gpu(golden_corr[f"{name}.coords{k}"])).cpu().numpy()
+        ref = golden_corr[f"{name}.lookup{k}"]
+        assert out.shape == ref.shape
+        assert np.abs(out - ref).max() <= 1e-5 * max(np.abs(ref).max(), 1.0)
+
+
+@pytest.mark.parametrize("hw", [(16, 16), (24, 24), (28, 28), (32, 32), (16, 40), (64, 64), (17, 21)])
+def test_lookup_bit_exact_on_oracle_pyramid(hw):
+    """Lookup isolated from GEMM precision: same fp32 pyramid on both sides."""
+    h, w = hw
+    b, c = (1, 8) if h * w > 2000 else (2, 8)
+    g = torch.Generator().manual_seed(h * 100 + w)
+    f1, f2 = torch.randn(b, c, h, w, generator=g), torch.randn(b, c, h, w, generator=g)
+    ref = corr_oracle.CorrBlock(f1, f2)
+    pyr = [p.numpy() for p in ref.corr_pyramid]
+    blk = cf.CorrBlock.from_pyramid([p.to(DEV) for p in ref.corr_pyramid], radius=4)
+    for kind, coords in _coord_sets(g, b, h, w).items():
+        out = blk(coords.to(DEV)).cpu().numpy()
+        want_c, ctaps, cidx = c_oracle.lookup(pyr, coords.numpy(), want_taps=True)
+        assert np.array_equal(out, want_c), kind                               # bit-exact vs the C oracle
+        want_t = ref(coords).numpy()
+        assert np.abs(out - want_t).max() <= 1e-5 * max(np.abs(want_t).max(), 1.0), kind
+        t, idx = cf.lookup_taps(coords.to(DEV))
+        assert np.array_equal(t.cpu().numpy(), ctaps) and np.array_equal(idx.cpu().numpy(), cidx), kind
+        if kind in ("far", "negfar"):
+            assert not out.any()
+
+
+@pytest.mark.parametrize("radius,levels", [(1, 4), (2, 3), (3, 2), (4, 1), (4, 5)])
+def test_other_radius_and_levels(radius, levels):
+    g = torch.Generator().manual_seed(radius * 10 + levels)
+    h = w = 32
+    f1, f2 = torch.randn(1, 8, h, w, generator=g), torch.randn(1, 8, h, w, generator=g)
+    ref = corr_oracle.CorrBlock(f1, f2, num_levels=levels, radius=radius)
+    blk = cf.CorrBlock.from_pyramid([p.to(DEV) for p in ref.corr_pyramid], radius=radius)
+    coords = corr_oracle.coords_grid(1, h, w) + torch.randn(1, 2, h, w, generator=g) * 3
+    out = blk(coords.to(DEV)).cpu().numpy()
+    assert out.shape == (1, levels * (2 * radius + 1) ** 2, h, w)
+    assert np.array_equal(out, c_oracle.lookup([p.numpy() for p in ref.corr_pyramid], coords.numpy(), radius=radius))
+    built = cf.CorrBlock(f1.to(DEV), f2.to(DEV), num_levels=levels, radius=radius, precision="fp32")
+    assert len(built.corr_pyramid) == levels
+    assert np.abs(built(coords.to(DEV)).cpu().numpy() - ref(coords).numpy()).max() <= 1e-5 * 4
+
+
+def test_window_orientation_anisotropic():
+    """Channel i*9+j must sample (x + i - r, y + j - r): a ramp in x only tells the two axes apart."""
+    h = w = 16
+    lvl0 = torch.arange(w, dtype=torch.float32).view(1, 1, 1, w).repeat(h * w, 1, h, 1)
+    pyr = [lvl0]
+    for _ in range(3):
+        pyr.append(torch.nn.functional.avg_pool2d(pyr[-1], 2, stride=2))
+    blk = cf.CorrBlock.from_pyramid([p.to(DEV) for p in pyr])
+    coords = torch.full((1, 2, h, w), 8.0)
+    out = blk(coords.to(DEV)).cpu().view(4, 9, 9, h, w)
+    lvl = out[0, :, :, 5, 5]
+    assert torch.allclose(lvl[:, 0], torch.arange(4.0, 13.0), atol=1e-5)   # varies along i (x offset)
+    assert torch.allclose(lvl[3, :], torch.full((9,), 7.0), atol=1e-5)     # constant along j (y offset)
+
+
+@pytest.mark.parametrize("hw,c", [((32, 32), 256), ((28, 28), 256), ((24, 24), 64), ((16, 16), 256), ((64, 64), 128)])
+def test_correlation_precisions(hw, c):
+    h, w = hw
+    g = torch.Generator().manual_seed(c + h)
+    f1, f2 = torch.randn(2, c, h, w, generator=g), torch.randn(2, c, h, w, generator=g)
+    ref = corr_oracle.CorrBlock(f1, f2)
+    exact = cf.CorrBlock(f1.to(DEV), f2.to(DEV), precision="fp32")
+    for lvl in range(4):
+        assert rel_err(exact.corr_pyramid[lvl].cpu().numpy(), ref.corr_pyramid[lvl].numpy()) <= 1e-5
+    auto = cf.CorrBlock(f1.to(DEV), f2.to(DEV))      # tensor cores when the shape allows
+    for lvl in range(4):
+        assert rel_err(auto.corr_pyramid[lvl].cpu().numpy(), ref.corr_pyramid[lvl].numpy()) <= 1e-2
+        if lvl:
+            assert np.array_equal(auto.corr_pyramid[lvl].cpu().numpy()[:, 0],
+                                  taps.avg_pool2x2(auto.corr_pyramid[lvl - 1].cpu().numpy()[:, 0]))
+
+
+def test_twelve_iteration_trajectory_cfg1():
+    """BASELINE cfg 1: 256-ch 28x28 fmaps, 4 levels, radius 4, 12 lookups along a synthetic trajectory."""
+    g = torch.Generator().manual_seed(1001)
+    f1, f2 = torch.randn(1, 256, 28, 28, generator=g), torch.randn(1, 256, 28, 28, generator=g)
+    ref = corr_oracle.CorrBlock(f1, f2)
+    blk = cf.CorrBlock(f1.to(DEV), f2.to(DEV), radius=4, precision="fp32")
+    coords = corr_oracle.coords_grid(1, 28, 28)
+    gpu_grid = cf.coords_grid(1, 28, 28, device=DEV)
+    assert torch.equal(gpu_grid.cpu(), coords)
+    for k in range(12):
+        out = blk(coords.to(DEV)).cpu().numpy()
+        want = ref(coords).numpy()
+        assert np.abs(out - want).max() <= 2e-5 * np.abs(want).max(), k      # fp32 GEMM order + lookup
+        coords = (coords + torch.randn(1, 2, 28, 28, generator=g) * 0.5 * (k + 1))
+        coords[:, 0].clamp_(-4, 32)
+        coords[:, 1].clamp_(-4, 32)
+
+
+def test_torchvision_call_site_adaptor():
+    """The reference's in-tree third-party call site (nnMTLTrainerV2Raft.py:97-118): raft_large's corr_block
+    replaced by an adaptor over the new kernels must reproduce the 12-iteration flow predictions."""
+    from torchvision.models.optical_flow import raft_large
+    torch.manual_seed(0)
+    model = raft_large(weights=None).to(DEV).eval()
+    img1, img2 = torch.rand(1, 3, 128, 128, device=DEV) * 2 - 1, torch.rand(1, 3, 128, 128, device=DEV) * 2 - 1
+    with torch.no_grad():
+        want = model(img1, img2, num_flow_updates=12)
+
+        class Adaptor(torch.nn.Module):
+            out_channels = model.corr_block.out_channels
+            num_levels, radius = 4, 4
+
+            def build_pyramid(self, fmap1, fmap2):
+                self.blk = cf.CorrBlock(fmap1, fmap2, num_levels=4, radius=4, precision="fp32")
+
+            def index_pyramid(self, coords):
+                return self.blk(coords)
+
+        model.corr_block = Adaptor()
+        got = model(img1, img2, num_flow_updates=12)
+    for a, b in zip(got, want):
+        assert float((a - b).abs().max()) <= 1e-3 * max(float(b.abs().max()), 1.0)
+
+
+def test_full_size_properties_cfg4():
+    """BASELINE cfg 4 size (64x64 fmaps, 16.7M-entry volume per pair): properties + a sampled oracle check."""
+    g = torch.Generator(device=DEV).manual_seed(1004)
+    b, c, h, w = 4, 256, 64, 64
+    f1 = torch.randn(b, c, h, w, device=DEV, generator=g)
+    f2 = torch.randn(b, c, h, w, device=DEV, generator=g)
+    blk = cf.CorrBlock(f1, f2, precision="fp32")
+    grid = cf.coords_grid(b, h, w, device=DEV)
+    out = blk(grid).view(b, 4, 9, 9, h * w)
+    # centre tap of level 0 at integer coords == corr[p, p] (diagonal of the volume), up to the round trip
+    diag = torch.einsum("bcp,bcp->bp", f1.view(b, c, -1), f2.view(b, c, -1)) / 16.0
+    assert float((out[:, 0, 4, 4] - diag).abs().max()) <= 1e-4 * float(diag.abs().max())
+    assert not bool(blk(grid + 5000.0).any())
+    # linearity in fmap2: corr(f1, a*f2 + f2') lookups == a*lookup + lookup'
+    f2b = torch.randn(b, c, h, w, device=DEV, generator=g)
+    coords = grid + torch.randn(b, 2, h, w, device=DEV, generator=g) * 2
+    lhs = cf.CorrBlock(f1, 0.5 * f2 + f2b, precision="fp32")(coords)
+    rhs = 0.5 * blk(coords) + cf.CorrBlock(f1, f2b, precision="fp32")(coords)
+    assert float((lhs - rhs).abs().max()) <= 1e-4 * float(rhs.abs().max())
+    ref = corr_oracle.CorrBlock(f1[:1].cpu(), f2[:1].cpu())
+    want = ref(coords[:1].cpu()).numpy()
+    assert np.abs(blk(coords)[:1].cpu().numpy() - want).max() <= 2e-5 * np.abs(want).max()

@@ -1,0 +1,111 @@
+"""GPU parity: the warp kernels (through the C ABI / module API) against the oracle and the golden vectors.
+
+Tolerances: tap coordinates bit-exact; bilinear values bit-exact against the C oracle (same op order, fmaf as
+ATen's CUDA kernel) and <= 1e-5 relative (max|diff| / max|ref|) against torch's CPU grid_sample / fixtures.
+"""
+import numpy as np
+import pytest
+import torch
+
+import cardioflow_b200 as cf
+from conftest import WARP_CASES, rel_err
+from oracle import c_oracle, taps, warp_oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _gpu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+@pytest.mark.parametrize("name", WARP_CASES)
+def test_golden_fixture(golden_warp, name):
+    flow, src = golden_warp[f"{name}.flow"], golden_warp[f"{name}.src"]
+    st = cf.SpatialTransformer(flow.shape[2:]).to(DEV)
+    out = st(flow=_gpu(flow), original=_gpu(src)).cpu().numpy()
+    assert rel_err(out, golden_warp[f"{name}.bilinear"]) <= 1e-5
+    assert np.array_equal(out, c_oracle.warp2d(flow, src))
+    t = cf.warp_taps(_gpu(flow)).cpu().numpy()
+    nt = taps.warp_taps(flow)
+    assert np.array_equal(t[:, 0], nt["uy"]) and np.array_equal(t[:, 1], nt["ux"])
+    near = cf.SpatialTransformer(flow.shape[2:], mode="nearest").to(DEV)(_gpu(flow), _gpu(src)).cpu().numpy()
+    assert np.array_equal(near, golden_warp[f"{name}.nearest"])
+
+
+@pytest.mark.parametrize("size", [(128, 128), (192, 192), (224, 224), (256, 256), (30, 45)])
+@pytest.mark.parametrize("chan", [1, 2, 4, 5])
+def test_shapes_and_flows(size, chan):
+    g = torch.Generator().manual_seed(size[0] * 10 + chan)
+    h, w = size
+    src = torch.rand(2, chan, h, w, generator=g)
+    flows = {
+        "zero": torch.zeros(2, 2, h, w),
+        "integer": torch.randint(-5, 6, (2, 2, h, w), generator=g).float(),
+        "half": torch.full((2, 2, h, w), -0.5),
+        "noise": torch.randn(2, 2, h, w, generator=g) * 3,
+        "large": torch.randn(2, 2, h, w, generator=g) * h,
+    }
+    st = cf.SpatialTransformer(size).to(DEV)
+    ref_mod = warp_oracle.SpatialTransformer(size)
+    for kind, flow in flows.items():
+        out = st(flow.to(DEV), src.to(DEV)).cpu()
+        ref = ref_mod(flow, src)
+        assert rel_err(out.numpy(), ref.numpy()) <= 1e-5, kind
+        if chan == 1:
+            assert np.array_equal(out.numpy(), c_oracle.warp2d(flow.numpy(), src.numpy())), kind
+
+
+def test_module_api_quirks():
+    g = torch.Generator().manual_seed(3)
+    flow, src = torch.randn(1, 2, 32, 32, generator=g) * 2, torch.rand(1, 3, 32, 32, generator=g)
+    st = cf.SpatialTransformer((32, 32))
+    st = st.to(DEV)
+    assert st.grid.is_cuda
+    a = st(flow=flow.to(DEV), original=src.to(DEV))
+    b = st(flow.to(DEV), src.to(DEV), mode="nearest")           # forward's mode is ignored (integration.py:79)
+    assert torch.equal(a, b)
+    c = cf.warp(src.to(DEV), flow.to(DEV))                       # voxelmorph-order alias
+    assert torch.equal(a, c)
+    nc = src.to(DEV).permute(0, 1, 3, 2).contiguous().permute(0, 1, 3, 2)   # non-contiguous input
+    assert torch.equal(st(flow.to(DEV), nc), a)
+    with pytest.raises(ValueError):
+        st(torch.zeros(1, 2, 16, 16, device=DEV), torch.zeros(1, 1, 16, 16, device=DEV))
+    flow_before = flow.to(DEV).clone()
+    fl = flow_before.clone()
+    st(fl, src.to(DEV))
+    assert torch.equal(fl, flow_before)                          # inputs are not modified
+
+
+def test_onehot_argmax(golden_warp):
+    flow, label = golden_warp["argmax.flow"], golden_warp["argmax.label"]
+    out = cf.warp_onehot_argmax(_gpu(flow), _gpu(label), 4).cpu().numpy()
+    assert np.array_equal(out, golden_warp["argmax.out"])
+    g = torch.Generator().manual_seed(11)
+    label = torch.randint(0, 4, (3, 1, 224, 224), generator=g)
+    flow = torch.randn(3, 2, 224, 224, generator=g) * 4
+    out = cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV)).cpu()
+    assert torch.equal(out, warp_oracle.warp_onehot_argmax(flow, label))
+    # and it equals the unfused module path on the device
+    onehot = torch.nn.functional.one_hot(label[:, 0], 4).permute(0, 3, 1, 2).contiguous().float().to(DEV)
+    unfused = torch.argmax(cf.SpatialTransformer((224, 224)).to(DEV)(flow.to(DEV), onehot), dim=1, keepdim=True)
+    assert torch.equal(out, unfused.cpu())
+
+
+def test_full_size_properties_cfg3():
+    """BASELINE cfg 3 size (300 x (1+4) x 224^2): size-independent properties instead of a CPU oracle."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    src = torch.rand(300, 5, 224, 224, device=DEV, generator=g)
+    st = cf.SpatialTransformer((224, 224)).to(DEV)
+    ident = st(torch.zeros(300, 2, 224, 224, device=DEV), src)
+    assert float((ident - src).abs().max()) <= 1e-6             # zero flow = identity up to the fp32 round trip
+    flow = torch.randn(300, 2, 224, 224, device=DEV, generator=g) * 3
+    other = torch.rand(300, 5, 224, 224, device=DEV, generator=g)
+    lin = st(flow, 2.0 * src + other)
+    assert float((lin - (2.0 * st(flow, src) + st(flow, other))).abs().max()) <= 1e-5      # linear in the source
+    shift = torch.zeros(300, 2, 224, 224, device=DEV)
+    shift[:, 1] = 1000.0
+    assert float(st(shift, src).abs().max()) == 0.0             # far out of range -> zero padding
+    sub = slice(0, 2)
+    ref = warp_oracle.SpatialTransformer((224, 224))(flow[sub].cpu(), src[sub].cpu())
+    assert rel_err(st(flow[sub], src[sub]).cpu().numpy(), ref.numpy()) <= 1e-5

@@ -1,0 +1,119 @@
+"""CPU: pin the oracle (three restatements) to the golden vectors frozen from the real reference."""
+import importlib.util
+import os
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import CORR_CASES, WARP_CASES, rel_err
+from oracle import c_oracle, corr_oracle, taps, warp_oracle
+
+REF_FILE = "/root/reference/nnunet/network_architecture/integration.py"
+
+
+@pytest.mark.parametrize("name", WARP_CASES)
+def test_warp_restatements_match_reference_fixture(golden_warp, name):
+    flow, src = golden_warp[f"{name}.flow"], golden_warp[f"{name}.src"]
+    ref = golden_warp[f"{name}.bilinear"]
+    size = flow.shape[2:]
+    t = warp_oracle.SpatialTransformer(size)(flow=torch.from_numpy(flow), original=torch.from_numpy(src)).numpy()
+    assert np.array_equal(t, ref)                      # torch restatement: bit-exact with the reference module
+    assert rel_err(taps.warp_from_taps(flow, src), ref) < 1e-6
+    c, ctaps = c_oracle.warp2d(flow, src, want_taps=True)
+    assert rel_err(c, ref) < 1e-6
+    nt = taps.warp_taps(flow)
+    assert np.array_equal(ctaps[:, 0], nt["uy"]) and np.array_equal(ctaps[:, 1], nt["ux"])
+    near = warp_oracle.SpatialTransformer(size, mode="nearest")(torch.from_numpy(flow), torch.from_numpy(src)).numpy()
+    assert np.array_equal(near, golden_warp[f"{name}.nearest"])
+    assert np.array_equal(c_oracle.warp2d(flow, src, mode="nearest"), golden_warp[f"{name}.nearest"])
+
+
+def test_forward_mode_argument_is_ignored(golden_warp):
+    flow, src = torch.from_numpy(golden_warp["noise_48.flow"]), torch.from_numpy(golden_warp["noise_48.src"])
+    st = warp_oracle.SpatialTransformer((48, 48))
+    assert torch.equal(st(flow, src, mode="nearest"), st(flow, src))
+
+
+def test_state_dict_grid(golden_warp):
+    st = warp_oracle.SpatialTransformer((6, 5))
+    assert list(st.state_dict().keys()) == ["grid"]
+    assert np.array_equal(st.state_dict()["grid"].numpy(), golden_warp["state.grid_6x5"])
+
+
+def test_onehot_argmax_vecint_contour(golden_warp):
+    flow, label = golden_warp["argmax.flow"], golden_warp["argmax.label"]
+    assert np.array_equal(warp_oracle.warp_onehot_argmax(torch.from_numpy(flow), torch.from_numpy(label)).numpy(),
+                          golden_warp["argmax.out"])
+    assert np.array_equal(c_oracle.warp_onehot_argmax(flow, label), golden_warp["argmax.out"])
+    vec = torch.from_numpy(golden_warp["vecint.vec"])
+    assert np.array_equal(warp_oracle.VecInt((32, 32), 7)(vec).numpy(), golden_warp["vecint.out7"])
+    locs = torch.from_numpy(golden_warp["contour.locs"]).clone()
+    out = warp_oracle.SpatialTransformerContour((32, 32))(locs, torch.from_numpy(golden_warp["contour.field"]))
+    assert np.array_equal(out.numpy(), golden_warp["contour.out"])
+    assert float(locs.abs().max()) <= 1.0 + 1e-6     # argument normalised in place, like the reference
+
+
+@pytest.mark.parametrize("name", CORR_CASES)
+def test_corr_restatements_match_torchvision_fixture(golden_corr, name):
+    f1, f2 = golden_corr[f"{name}.f1"], golden_corr[f"{name}.f2"]
+    blk = corr_oracle.CorrBlock(torch.from_numpy(f1), torch.from_numpy(f2), num_levels=4, radius=4)
+    pyr = [p.numpy() for p in blk.corr_pyramid]
+    cpyr = c_oracle.build_pyramid(f1, f2)
+    assert rel_err(cpyr[0], pyr[0]) < 1e-5            # different summation order than BLAS
+    for lvl in (1, 2, 3):
+        assert np.array_equal(pyr[lvl], golden_corr[f"{name}.pyr{lvl}"])
+        assert np.array_equal(taps.avg_pool2x2(pyr[lvl - 1][:, 0]), golden_corr[f"{name}.pyr{lvl}"][:, 0])
+        assert np.array_equal(c_oracle.avg_pool2x2(pyr[lvl - 1]), golden_corr[f"{name}.pyr{lvl}"])
+    for k in range(4):
+        coords, ref = golden_corr[f"{name}.coords{k}"], golden_corr[f"{name}.lookup{k}"]
+        assert np.array_equal(blk(torch.from_numpy(coords)).numpy(), ref)
+        c, ctaps, cidx = c_oracle.lookup(pyr, coords, want_taps=True)
+        scale = max(np.abs(ref).max(), 1.0)
+        assert np.abs(c - ref).max() / scale < 1e-6
+        assert np.abs(taps.lookup_from_taps(pyr, coords) - ref).max() / scale < 1e-6
+        nt = taps.lookup_taps(coords, [p.shape[-2:] for p in pyr])
+        for lvl in range(4):
+            assert np.array_equal(ctaps[lvl][:, 0], nt[lvl]["ux"]) and np.array_equal(ctaps[lvl][:, 1], nt[lvl]["uy"])
+            assert np.array_equal(cidx[lvl][:, 0], nt[lvl]["x0"]) and np.array_equal(cidx[lvl][:, 1], nt[lvl]["y0"])
+    assert not golden_corr[f"{name}.lookup3"].any()   # far out-of-range coords -> zeros
+
+
+def test_round_trip_is_not_identity():
+    """integer coordinates can land one ulp below the integer -> floor flips."""
+    for size in (28, 64, 256):
+        p = np.arange(-4, size + 4, dtype=np.float32)
+        u = taps.lookup_coord(p, size)
+        assert (np.floor(u) != p).any()
+
+
+def test_coords_grid_and_errors():
+    g = corr_oracle.coords_grid(2, 3, 5)
+    assert g.shape == (2, 2, 3, 5) and g[1, 0, 2, 4] == 4 and g[1, 1, 2, 4] == 2
+    with pytest.raises(ValueError):
+        corr_oracle.CorrBlock(torch.zeros(1, 4, 8, 8), torch.zeros(1, 4, 8, 8))       # too small for 4 levels
+    with pytest.raises(ValueError):
+        corr_oracle.CorrBlock(torch.zeros(1, 4, 16, 16), torch.zeros(1, 4, 16, 24))
+
+
+@pytest.mark.skipif(not os.path.exists(REF_FILE), reason="reference tree not present (GPU box)")
+def test_live_reference_agrees_with_oracle():
+    spec = importlib.util.spec_from_file_location("ref_integration", REF_FILE)
+    ref = importlib.util.module_from_spec(spec)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        spec.loader.exec_module(ref)
+        g = torch.Generator().manual_seed(7)
+        flow = torch.randn(2, 2, 40, 56, generator=g) * 4
+        src = torch.rand(2, 3, 40, 56, generator=g)
+        a = ref.SpatialTransformer((40, 56))(flow=flow.clone(), original=src)
+    b = warp_oracle.SpatialTransformer((40, 56))(flow=flow, original=src)
+    assert torch.equal(a, b)
+    from torchvision.models.optical_flow.raft import CorrBlock as TV
+    f1, f2 = torch.randn(1, 16, 16, 20, generator=g), torch.randn(1, 16, 16, 20, generator=g)
+    tv = TV(num_levels=4, radius=4)
+    tv.build_pyramid(f1, f2)
+    mine = corr_oracle.CorrBlock(f1, f2)
+    coords = corr_oracle.coords_grid(1, 16, 20) + torch.randn(1, 2, 16, 20, generator=g) * 2
+    assert torch.equal(tv.index_pyramid(coords), mine(coords))

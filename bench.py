@@ -195,7 +195,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="auto", choices=["auto", "tf32", "fp32"])
+    ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp32"])
     ap.add_argument("--graph", action="store_true", help="replay each step as one CUDA graph")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -352,7 +352,7 @@ def main():
     line = {
         "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32" if used_precision == "fp32" else "tf32 GEMM / f32 lookup+warp",
+        "vs_baseline": None, "dtype": "f32" if used_precision == "fp32" else "bf16 GEMM (fp32 accumulate) / f32 lookup+warp",
         "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step_per_gpu": P,
                    "corr_precision": used_precision, "cuda_graph": bool(graphs),

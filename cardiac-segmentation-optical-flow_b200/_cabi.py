@@ -10,9 +10,9 @@ LIB_PATH = os.path.join(PKG, "libcardioflow.so")
 HEADER = os.path.join(os.path.dirname(PKG), "include", "cardioflow.h")
 
 CF_OK, CF_ERR_BAD_ARG, CF_ERR_UNSUPPORTED, CF_ERR_CUDA = 0, -1, -2, -3
-PREC_TF32, PREC_FP32, PREC_AUTO = 0, 1, 2
+PREC_BF16, PREC_FP32, PREC_AUTO = 0, 1, 2
 MODE_BILINEAR, MODE_NEAREST = 0, 1
-PRECISIONS = {"tf32": PREC_TF32, "fp32": PREC_FP32, "auto": PREC_AUTO}
+PRECISIONS = {"bf16": PREC_BF16, "fp32": PREC_FP32, "auto": PREC_AUTO}
 
 _c = ctypes
 _P, _I, _Z = _c.c_void_p, _c.c_int, _c.c_size_t
@@ -23,7 +23,8 @@ _SIGNATURES = {
     "cf_corr_pyramid_level_offset": (_Z, [_I, _I, _I, _I]),
     "cf_corr_pyramid_bytes": (_Z, [_I, _I, _I, _I]),
     "cf_coords_grid": (_I, [_P, _I, _I, _I, _P]),
-    "cf_corr_build": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _c.POINTER(_I), _P]),
+    "cf_corr_build_workspace_bytes": (_Z, [_I, _I, _I, _I, _I]),
+    "cf_corr_build": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _Z, _c.POINTER(_I), _P]),
     "cf_corr_pool": (_I, [_P, _I, _I, _I, _I, _I, _P]),
     "cf_corr_lookup": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "cf_corr_lookup_taps": (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),

@@ -36,6 +36,22 @@ def _level_views(pyramid, B, H, W, L):
     return views
 
 
+_WORKSPACES = {}
+
+
+def _workspace(device, nbytes):
+    """Per-device scratch for the bf16 copies of the feature maps (stream-ordered reuse: every use is enqueued
+    on the current stream before the next one)."""
+    if nbytes == 0:
+        return None
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _WORKSPACES.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _WORKSPACES[key] = buf
+    return buf
+
+
 class _CorrBuild(torch.autograd.Function):
     """(fmap1, fmap2) -> packed pyramid.  a2 + a3 of SURVEY.md 8(a)."""
 
@@ -52,9 +68,12 @@ class _CorrBuild(torch.autograd.Function):
         else:
             pyramid = pyramid.view(-1)[:nfloats]
         used = _cabi.ctypes.c_int(-1)
+        ws_bytes = lib.cf_corr_build_workspace_bytes(B, C, H, W, precision)
+        ws = _workspace(f1.device, ws_bytes)
         with torch.cuda.device(f1.device):
             _cabi.check(lib.cf_corr_build(f1.data_ptr(), f2.data_ptr(), B, C, H, W, num_levels, precision,
-                                          pyramid.data_ptr(), _cabi.ctypes.byref(used), _cabi.stream()), "cf_corr_build")
+                                          pyramid.data_ptr(), ws.data_ptr() if ws is not None else None, ws_bytes,
+                                          _cabi.ctypes.byref(used), _cabi.stream()), "cf_corr_build")
         ctx.save_for_backward(f1, f2)
         ctx.meta = (B, C, H, W, num_levels)
         ctx.used_precision = used.value
@@ -112,7 +131,7 @@ class _CorrLookup(torch.autograd.Function):
 class CorrBlock:
     """Drop-in for RAFT's ``CorrBlock(fmap1, fmap2, num_levels=4, radius=4)``; instances are callable.
 
-    ``precision``: "tf32" (tcgen05 tensor cores), "fp32" (CUDA cores, exact-precision mode) or "auto"
+    ``precision``: "bf16" (tcgen05 tensor cores, fp32 accumulate), "fp32" (CUDA cores, exact-precision mode) or "auto"
     (default; env ``CARDIOFLOW_CORR_PRECISION``).  ``pyramid_buffer`` / ``out=`` let a caller that loops over
     frame pairs reuse device memory (the reference allocates afresh every call).  Errors follow torchvision raft.py:368-383 (ValueError).
     """
@@ -136,7 +155,7 @@ class CorrBlock:
         B, _, H, W = fmap1.shape
         self._meta = (B, H, W, num_levels, radius)
         self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer)
-        self.used_precision = {0: "tf32", 1: "fp32"}.get(getattr(_CorrBuild, "last_used_precision", -1), "?")
+        self.used_precision = {0: "bf16", 1: "fp32"}.get(getattr(_CorrBuild, "last_used_precision", -1), "?")
         self.corr_pyramid = _level_views(self._pyramid, B, H, W, num_levels)
 
     @classmethod

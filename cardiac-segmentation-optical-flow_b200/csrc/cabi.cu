@@ -52,7 +52,12 @@ int check_corr_shape(int B, int H, int W, int L, LevelDims* d) {
 
 using namespace cf;
 
+namespace cf { void corr_tcgen05_set_debug(float* p); }
+
 extern "C" {
+
+// bring-up hook, not part of the public header
+CF_API void cf_debug_set_gemm_dump(float* p) { cf::corr_tcgen05_set_debug(p); }
 
 int cf_version(void) { return 100; }
 
@@ -78,12 +83,17 @@ int cf_coords_grid(float* out, int B, int H, int W, void* stream) {
     return launch_coords_grid(out, B, H, W, (cudaStream_t)stream);
 }
 
+size_t cf_corr_build_workspace_bytes(int B, int C, int H, int W, int precision) {
+    if (precision == CF_PREC_FP32 || B < 1 || C < 1 || H < 1 || W < 1) return 0;
+    return (corr_tcgen05_supported(B, C, H, W, false)) ? corr_tcgen05_workspace_bytes(B, C, H, W) : 0;
+}
+
 int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
-                  float* pyramid, int* used_precision, void* stream) {
+                  float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision, void* stream) {
     CF_REQUIRE(f1 && f2 && pyramid, CF_ERR_BAD_ARG, "cf_corr_build: null pointer");
     CF_REQUIRE(C > 0, CF_ERR_BAD_ARG, "cf_corr_build: C must be positive");
     CF_REQUIRE(((uintptr_t)pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_build: pyramid must be 256-byte aligned");
-    CF_REQUIRE(precision == CF_PREC_TF32 || precision == CF_PREC_FP32 || precision == CF_PREC_AUTO, CF_ERR_BAD_ARG,
+    CF_REQUIRE(precision == CF_PREC_BF16 || precision == CF_PREC_FP32 || precision == CF_PREC_AUTO, CF_ERR_BAD_ARG,
                "cf_corr_build: unknown precision %d", precision);
     LevelDims d;
     int rc = check_corr_shape(B, H, W, L, &d);
@@ -98,15 +108,15 @@ int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, 
         const bool fuse = level1 && corr_tcgen05_supported(B, C, H, W, true) && aligned16(f1) && aligned16(f2);
         const bool plain = !fuse && corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2);
         if (fuse || plain) {
-            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, level0, fuse ? level1 : nullptr, s);
+            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, level0, fuse ? level1 : nullptr, workspace, workspace_bytes, s);
             if (rc) return rc;
-            used = CF_PREC_TF32;
+            used = CF_PREC_BF16;
             from_level = fuse ? 1 : 0;
-        } else if (precision == CF_PREC_TF32) {
+        } else if (precision == CF_PREC_BF16) {
             return fail(CF_ERR_UNSUPPORTED,
                         "cf_corr_build: shape B=%d C=%d H=%d W=%d does not fit the tcgen05 tiling "
-                        "(need H*W %% 4 == 0, C %% 8 == 0, 16-byte aligned inputs); use CF_PREC_AUTO or CF_PREC_FP32",
-                        B, C, H, W);
+                        "(need H*W %% 8 == 0, C %% 16 == 0, C <= 256, 16-byte aligned inputs); use CF_PREC_AUTO or "
+                        "CF_PREC_FP32", B, C, H, W);
         }
     }
     if (used == CF_PREC_FP32) {

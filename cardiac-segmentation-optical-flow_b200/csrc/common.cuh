@@ -82,7 +82,9 @@ int launch_pool_chain_bwd(float* gpyr, const LevelDims& d, long n_img, int L, cu
 int launch_corr_simt(const float* f1, const float* f2, int B, int C, int HW, float* level0, cudaStream_t s);
 // returns CF_ERR_UNSUPPORTED (without touching the stream) when the shape does not fit the TMA/UMMA tiling
 int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* level0,
-                        float* level1 /* may be null: no fused pooling */, cudaStream_t s);
+                        float* level1 /* may be null: no fused pooling */, void* workspace, size_t ws_bytes,
+                        cudaStream_t s);
+size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W);
 bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool);
 int launch_corr_volume_bwd(const float* f1, const float* f2, const float* gcorr, int B, int C, int HW,
                            float* gf1, float* gf2, cudaStream_t s);

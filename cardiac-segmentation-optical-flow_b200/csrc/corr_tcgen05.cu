@@ -1,0 +1,479 @@
+// K1: all-pairs correlation as a TMA-fed tcgen05 (5th-gen tensor core) GEMM with a fused epilogue.
+//
+//   corr[b, p, q] = <f1[b, :, p], f2[b, :, q]> / sqrt(C)          level 0  [B*HW, 1, H, W]
+//   level1[b, p]  = avg_pool2d(corr[b, p], 2, 2)                   level 1  [B*HW, 1, H/2, W/2]  (fused)
+//
+// Replaces torchvision raft.py:424-431 + the first avg_pool2d of raft.py:390-392 (call site
+// /root/reference/nnunet/network_architecture/SegFlowGaussian.py:929): there a cuBLAS batched SGEMM, a
+// separate elementwise division over the whole volume and a pooling launch that re-reads it.
+//
+// Mapping to the hardware
+//   * A = f1[b]^T and B = f2[b] are both stored [C, HW] with HW contiguous, i.e. "MN-major" operands.  Measured
+//     on B200 (tools/umma_probe.cu): tcgen05 kind::tf32 returns ZEROS for MN-major operands, kind::f16 (bf16)
+//     handles them.  So a tiny elementwise pre-pass rounds both maps to bf16 IN THE SAME LAYOUT (no transpose)
+//     and the MMA reads them as MN-major: TMA boxes of 64 positions x k rows land in shared memory with the
+//     128-byte swizzle, which is exactly the canonical MN-major SWIZZLE_128B UMMA layout (8 k-rows x 128 B
+//     atoms; LBO = stride between 64-position chunks, SBO = 1024 B between k-atoms).  fp32 accumulate in TMEM.
+//   * one CTA owns a 128-row block of queries p for one frame pair: the A block (128 x C bf16 = 64 KB at
+//     C = 256) is loaded ONCE and stays resident; B streams through a 4-stage ring of 128(n) x 64(k) tiles;
+//     accumulators (128 x BN fp32) are double-buffered in TMEM so the epilogue of tile t overlaps the MMAs of
+//     tile t+1.  Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-5 =
+//     epilogue (tcgen05.ld -> scale -> swizzled smem -> TMA store of level 0; second TMEM pass pools 2x2 over
+//     the (h2, w2) axes and stores level 1 directly).
+//   * BN = 2*W*k so that a tile covers whole pairs of image rows of fmap2 (the pooling window never crosses a
+//     tile); the divide and the ((a+b)+c)+d)/4 order match ATen bit-for-bit given the fp32 accumulators.
+// The kernel is output-write bound (K = C = 256 only): 64 KB of level 0 + 16 KB of level 1 per 128x128 tile.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace cf {
+namespace {
+
+constexpr int BM = 128;        // query rows per CTA (UMMA M)
+constexpr int BK = 64;         // k rows per B stage (4 MMAs of K = 16)
+constexpr int UK = 16;         // K of one kind::f16 MMA
+constexpr int CHUNK = 64;      // positions per 128-byte swizzle row (bf16)
+constexpr int NSTAGE = 4;
+constexpr int EPI_WARPS = 4;
+constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
+constexpr int MAX_C = 256;     // A block resident in smem: C * 256 B
+constexpr int MAX_BN = 128;
+constexpr int TMEM_COLS = 256; // 2 accumulators x MAX_BN columns
+
+struct GemmParams {
+    float* level1;       // null -> no fused pooling
+    int C, HW, H, W;
+    int BN;              // tile width (multiple of 64, <= 128)
+    int n_tiles;         // ceil(HW / BN)
+    int n_split;         // CTAs per (b, m-tile) along n
+    int m_tiles;
+    float div;           // sqrt(C)
+    float mul;           // 1/div when that is exact (power of two), else 0
+    float* dbg;          // bring-up only: raw accumulators + smem operand dump of CTA 0 (null in production)
+};
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded spin: a protocol bug traps (launch error on the host) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    uint32_t spins = 0;
+    do {
+        if (++spins == (1u << 28)) __trap();
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory"); }
+
+// UMMA shared-memory descriptor, MN-major operand, SWIZZLE_128B (cute/arch/mma_sm100_desc.hpp bit layout)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46) /* sm_100 descriptor version */ |
+           (2ull << 61) /* SWIZZLE_128B */;
+}
+// instruction descriptor: D = f32, A = B = bf16, both MN-major, M x N
+__device__ __forceinline__ uint32_t umma_idesc(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ float scale_val(float v, const GemmParams& P) {
+    return P.mul != 0.0f ? __fmul_rn(v, P.mul) : __fdiv_rn(v, P.div);
+}
+__device__ __forceinline__ float pool4(float a, float b, float c, float d) {
+    return __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(a, b), c), d), 0.25f);  // /4 is exact as *0.25
+}
+
+// ---------------------------------------------------------------- shared memory carve-up (dynamic, 1024-aligned)
+struct SmemLayout {
+    uint32_t a;                 // [2 m-chunks][C rows][128 B]
+    uint32_t b0;                // NSTAGE x [BN/64 n-chunks][64 rows][128 B]
+    uint32_t epi0;              // 2 x [128 rows][128 B] swizzled staging for the level-0 TMA store
+    uint32_t bars;              // mbarriers
+    __device__ uint32_t b(int stage) const { return b0 + (uint32_t)stage * (MAX_BN * 128u); }
+    __device__ uint32_t epi(int i) const { return epi0 + (uint32_t)i * (128u * 128u); }
+};
+constexpr int kBarAFull = 0, kBarBFull = 1, kBarBEmpty = 1 + NSTAGE, kBarAccFull = 1 + 2 * NSTAGE,
+              kBarAccEmpty = 3 + 2 * NSTAGE, kNumBars = 5 + 2 * NSTAGE;
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint32_t tmem_base_slot;
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    SmemLayout S;
+    S.a = base;
+    S.b0 = base + (uint32_t)P.C * 256u;
+    S.epi0 = S.b0 + NSTAGE * MAX_BN * 128u;
+    S.bars = S.epi0 + 2u * 128u * 128u;
+    auto bar = [&](int i) { return S.bars + 8u * (uint32_t)i; };
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // work item: (b, m-tile, n-split)
+    const int split = blockIdx.x % P.n_split;
+    const int mt = (blockIdx.x / P.n_split) % P.m_tiles;
+    const int b = blockIdx.x / (P.n_split * P.m_tiles);
+    const int m0 = mt * BM;
+    const int tiles_per = (P.n_tiles + P.n_split - 1) / P.n_split;
+    const int nt_begin = split * tiles_per;
+    const int nt_end = min(P.n_tiles, nt_begin + tiles_per);
+    const int k_blocks = (P.C + BK - 1) / BK;
+    const int k_steps = P.C / UK;   // MMAs along K
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar(kBarAFull), 1);
+        for (int s = 0; s < NSTAGE; ++s) { mbar_init(bar(kBarBFull + s), 1); mbar_init(bar(kBarBEmpty + s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar(kBarAccFull + a), 1); mbar_init(bar(kBarAccEmpty + a), EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {  // TMEM allocation (one warp), address lands in shared memory
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(&tmem_base_slot)), "r"((uint32_t)TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            mbar_expect_tx(bar(kBarAFull), (uint32_t)P.C * 256u);
+            for (int mc = 0; mc < BM / CHUNK; ++mc)
+                tma_load_3d(S.a + (uint32_t)mc * (uint32_t)P.C * 128u, &tmA, bar(kBarAFull), m0 + mc * CHUNK, 0, b);
+            int stage = 0, phase = 0;
+            for (int nt = nt_begin; nt < nt_end; ++nt) {
+                const int n0 = nt * P.BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(bar(kBarBEmpty + stage), phase ^ 1);
+                    mbar_expect_tx(bar(kBarBFull + stage), (uint32_t)P.BN * 128u);
+                    for (int nc = 0; nc < P.BN / CHUNK; ++nc)
+                        tma_load_3d(S.b(stage) + (uint32_t)nc * (BK * 128u), &tmB, bar(kBarBFull + stage), n0 + nc * CHUNK,
+                                    kb * BK, b);
+                    if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc(BM, P.BN);
+            const uint32_t a_lbo = (uint32_t)P.C * 128u;  // stride between 64-row chunks of A
+            mbar_wait(bar(kBarAFull), 0);
+            tc_fence_after();
+            int stage = 0, phase = 0;
+            int t = 0;
+            for (int nt = nt_begin; nt < nt_end; ++nt, ++t) {
+                const int acc = t & 1;
+                mbar_wait(bar(kBarAccEmpty + acc), ((t >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + (uint32_t)(acc * MAX_BN);
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(bar(kBarBFull + stage), phase);
+                    tc_fence_after();
+                    const int nks = min(BK / UK, k_steps - kb * (BK / UK));
+                    for (int ks = 0; ks < nks; ++ks) {   // K = 16 per MMA = two 8-row swizzle atoms (2048 B)
+                        const uint64_t ad = umma_desc(S.a + (uint32_t)(kb * (BK / UK) + ks) * 2048u, a_lbo, 1024u);
+                        const uint64_t bd = umma_desc(S.b(stage) + (uint32_t)ks * 2048u, BK * 128u, 1024u);
+                        umma_bf16(d, ad, bd, idesc, (kb | ks) != 0);
+                    }
+                    umma_commit(bar(kBarBEmpty + stage));  // frees the stage when these MMAs retire
+                    if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(bar(kBarAccFull + acc));
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
+        const int row = quad * 32 + lane;                // accumulator row == query p - m0
+        const int ep_tid = (warp - 2) * 32 + lane;
+        const bool row_ok = (m0 + row) < P.HW;
+        const int W = P.W, W2 = P.W >> 1;
+        int t = 0, sb = 0;
+        for (int nt = nt_begin; nt < nt_end; ++nt, ++t) {
+            const int acc = t & 1;
+            const int n0 = nt * P.BN;
+            mbar_wait(bar(kBarAccFull + acc), (t >> 1) & 1);
+            tc_fence_after();
+            const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * MAX_BN);
+            if (P.dbg != nullptr && blockIdx.x == 0 && t == 0) {
+                for (int c = 0; c < P.BN / 32; ++c) {
+                    float v[32];
+                    tmem_ld32(tacc + (uint32_t)(c * 32), v);
+                    tmem_wait_ld();
+                    for (int i = 0; i < 32; ++i) P.dbg[row * 128 + c * 32 + i] = v[i];
+                }
+                const float* sa = reinterpret_cast<const float*>(smem_raw + (S.a - smem_u32(smem_raw)));
+                const float* sbp = reinterpret_cast<const float*>(smem_raw + (S.b0 - smem_u32(smem_raw)));
+                for (int i = ep_tid; i < P.C * 64; i += 128) P.dbg[16384 + i] = sa[i];
+                for (int i = ep_tid; i < MAX_BN * 32; i += 128) P.dbg[16384 + P.C * 64 + i] = sbp[i];
+                if (ep_tid == 0) { P.dbg[16384 + P.C * 64 + MAX_BN * 32] = __uint_as_float(tmem_base); }
+            }
+            // ---- pass 1: level 0, 32 columns at a time -> swizzled smem -> TMA store ----
+            for (int c = 0; c < P.BN / 32; ++c) {
+                float v[32];
+                tmem_ld32(tacc + (uint32_t)(c * 32), v);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = scale_val(v[i], P);
+                if (ep_tid == 0) tma_store_wait_read<1>();   // the store that used buffer `sb` two chunks ago is done
+                epi_bar_sync();
+                const uint32_t dst = S.epi(sb) + (uint32_t)row * 128u;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t addr = dst + (uint32_t)((j ^ (row & 7)) << 4);
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v[4 * j]), "f"(v[4 * j + 1]),
+                                 "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+                }
+                fence_async_smem();
+                epi_bar_sync();
+                if (ep_tid == 0) {
+                    tma_store_3d(&tmC, S.epi(sb), n0 + c * 32, m0, b);
+                    tma_store_commit();
+                }
+                sb ^= 1;
+            }
+            // ---- pass 2: fused level 1 = 2x2 average over the (h2, w2) axes of the scaled values ----
+            if (P.level1 != nullptr) {
+                const int pairs = P.BN / (2 * W);            // image-row pairs covered by this tile
+                const int pair0 = n0 / (2 * W);
+                float* l1row = P.level1 + ((size_t)b * P.HW + (size_t)(m0 + row)) * (size_t)((P.H >> 1) * W2);
+                for (int j = 0; j < pairs; ++j) {
+                    for (int m = 0; m < W / 8; ++m) {
+                        float top[8], bot[8];
+                        tmem_ld8(tacc + (uint32_t)((2 * j) * W + 8 * m), top);
+                        tmem_ld8(tacc + (uint32_t)((2 * j + 1) * W + 8 * m), bot);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { top[i] = scale_val(top[i], P); bot[i] = scale_val(bot[i], P); }
+                        float4 o;
+                        o.x = pool4(top[0], top[1], bot[0], bot[1]);
+                        o.y = pool4(top[2], top[3], bot[2], bot[3]);
+                        o.z = pool4(top[4], top[5], bot[4], bot[5]);
+                        o.w = pool4(top[6], top[7], bot[6], bot[7]);
+                        if (row_ok) *reinterpret_cast<float4*>(l1row + (size_t)(pair0 + j) * W2 + 4 * m) = o;
+                    }
+                }
+            }
+            // accumulator drained -> hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(kBarAccEmpty + acc));
+        }
+        if (ep_tid == 0) tma_store_wait_all();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------- host side
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeFn get_encode_fn() {
+    static EncodeFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeFn>(p);
+    });
+    return fn;
+}
+
+// 3-D tensor map: dims (d0 innermost), strides in bytes for d1, d2; 128-byte swizzle
+int make_map(CUtensorMap* m, CUtensorMapDataType dtype, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1,
+             uint64_t s2, uint32_t b0, uint32_t b1) {
+    EncodeFn enc = get_encode_fn();
+    if (!enc) return fail(CF_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    const cuuint64_t dims[3] = {d0, d1, d2};
+    const cuuint64_t strides[2] = {s1, s2};
+    const cuuint32_t box[3] = {b0, b1, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(m, dtype, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(CF_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return CF_OK;
+}
+
+// tile width for the fused-pool epilogue: BN = 2*W*k, multiple of CHUNK, <= MAX_BN, k | H/2
+int fused_bn(int H, int W) {
+    if ((H & 1) || (W & 7)) return 0;
+    int best = 0;
+    for (int k = 1; 2 * W * k <= MAX_BN; ++k)
+        if ((2 * W * k) % CHUNK == 0 && (H / 2) % k == 0) best = 2 * W * k;
+    return best;
+}
+
+// fp32 -> bf16 (round to nearest even), same [B, C, HW] layout; 8 elements per thread
+__global__ void __launch_bounds__(256) to_bf16_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                      __nv_bfloat16* __restrict__ oa, __nv_bfloat16* __restrict__ ob, long n8) {
+    const long i = (long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n8) return;
+    const float* src = blockIdx.y == 0 ? a : b;
+    __nv_bfloat16* dst = blockIdx.y == 0 ? oa : ob;
+    const float4 x = ldg_f4(src + 8 * i), y = ldg_f4(src + 8 * i + 4);
+    __nv_bfloat162 p0 = __floats2bfloat162_rn(x.x, x.y), p1 = __floats2bfloat162_rn(x.z, x.w);
+    __nv_bfloat162 p2 = __floats2bfloat162_rn(y.x, y.y), p3 = __floats2bfloat162_rn(y.z, y.w);
+    uint4 o;
+    o.x = *reinterpret_cast<uint32_t*>(&p0); o.y = *reinterpret_cast<uint32_t*>(&p1);
+    o.z = *reinterpret_cast<uint32_t*>(&p2); o.w = *reinterpret_cast<uint32_t*>(&p3);
+    *reinterpret_cast<uint4*>(dst + 8 * i) = o;
+}
+
+}  // namespace
+
+bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool) {
+    const long HW = (long)H * W;
+    if (B < 1 || C % UK != 0 || C > MAX_C || HW % 8 != 0 || HW < CHUNK) return false;
+    if (fuse_pool && fused_bn(H, W) == 0) return false;
+    return get_encode_fn() != nullptr;
+}
+
+static float* g_dbg = nullptr;
+void corr_tcgen05_set_debug(float* p) { g_dbg = p; }
+
+size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W) {
+    return 2 * round_up((size_t)B * C * H * W * sizeof(__nv_bfloat16), 256);
+}
+
+int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* level0, float* level1,
+                        void* workspace, size_t ws_bytes, cudaStream_t s) {
+    const int HW = H * W;
+    if (!workspace || ws_bytes < corr_tcgen05_workspace_bytes(B, C, H, W) || ((uintptr_t)workspace & 255u))
+        return fail(CF_ERR_BAD_ARG, "corr_tcgen05: workspace of %zu bytes (256-byte aligned) required, got %zu",
+                    corr_tcgen05_workspace_bytes(B, C, H, W), ws_bytes);
+    __nv_bfloat16* h1 = reinterpret_cast<__nv_bfloat16*>(workspace);
+    __nv_bfloat16* h2 = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(workspace) +
+                                                          round_up((size_t)B * C * HW * sizeof(__nv_bfloat16), 256));
+    {
+        const long n8 = (long)B * C * HW / 8;
+        dim3 grid((unsigned)cdiv(n8, 256), 2);
+        to_bf16_kernel<<<grid, 256, 0, s>>>(f1, f2, h1, h2, n8);
+        CF_CHECK_LAUNCH("to_bf16_kernel");
+    }
+    GemmParams P{};
+    P.level1 = level1;
+    P.C = C; P.HW = HW; P.H = H; P.W = W;
+    P.dbg = g_dbg;
+    P.BN = level1 ? fused_bn(H, W) : MAX_BN;
+    if (P.BN == 0) return fail(CF_ERR_UNSUPPORTED, "corr_tcgen05: %dx%d does not tile for the fused pooling epilogue", H, W);
+    P.n_tiles = (HW + P.BN - 1) / P.BN;
+    P.m_tiles = (HW + BM - 1) / BM;
+    P.div = sqrtf((float)C);
+    int e;
+    const float fr = frexpf(P.div, &e);
+    P.mul = (fr == 0.5f) ? 1.0f / P.div : 0.0f;  // power of two: scaling by the reciprocal is exact
+    // enough CTAs for ~3 waves over 148 SMs, but keep >= 2 tiles per CTA so the resident A block is amortised
+    int split = 1;
+    while ((long)B * P.m_tiles * split < 3 * 148 && P.n_tiles / (split * 2) >= 2) split *= 2;
+    P.n_split = split;
+
+    CUtensorMap tmA, tmB, tmC;
+    int rc;
+    const uint64_t sC = (uint64_t)HW * 2, sB = (uint64_t)C * HW * 2;
+    if ((rc = make_map(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, h1, HW, C, B, sC, sB, CHUNK, C))) return rc;
+    if ((rc = make_map(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, h2, HW, C, B, sC, sB, CHUNK, BK))) return rc;
+    if ((rc = make_map(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, level0, HW, HW, B, (uint64_t)HW * 4, (uint64_t)HW * HW * 4, 32,
+                       BM)))
+        return rc;
+
+    const size_t smem = 1024 + (size_t)C * 256 + (size_t)NSTAGE * MAX_BN * 128 + 2 * 128 * 128 + kNumBars * 8 + 64;
+    // opt in to the large dynamic shared memory once (sized for MAX_C; static smem counts against the 227 KB cap)
+    static std::once_flag attr_once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(attr_once, [] {
+        const int max_smem = 1024 + MAX_C * 256 + NSTAGE * MAX_BN * 128 + 2 * 128 * 128 + kNumBars * 8 + 64;
+        attr_err = cudaFuncSetAttribute(corr_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    });
+    if (attr_err != cudaSuccess) return fail(CF_ERR_CUDA, "cudaFuncSetAttribute(max smem): %s", cudaGetErrorString(attr_err));
+    const long grid = (long)B * P.m_tiles * P.n_split;
+    corr_tcgen05_kernel<<<(unsigned)grid, NTHREADS, smem, s>>>(tmA, tmB, tmC, P);
+    CF_CHECK_LAUNCH("corr_tcgen05_kernel");
+    return CF_OK;
+}
+
+}  // namespace cf

@@ -2,12 +2,6 @@
 // one by real implementations; each returns CF_ERR_UNSUPPORTED so a caller fails loudly).
 #include "common.cuh"
 using namespace cf;
-namespace cf {
-bool corr_tcgen05_supported(int, int, int, int, bool) { return false; }
-int launch_corr_tcgen05(const float*, const float*, int, int, int, int, float*, float*, cudaStream_t) {
-    return fail(CF_ERR_UNSUPPORTED, "tcgen05 correlation kernel not built");
-}
-}
 extern "C" {
 size_t cf_fmap_pyramid_level_offset(int, int, int, int, int) { return 0; }
 size_t cf_fmap_pyramid_bytes(int, int, int, int, int) { return 0; }

@@ -39,9 +39,9 @@ extern "C" {
 #define CF_MAX_RADIUS 4
 
 /* cf_corr_build precision */
-#define CF_PREC_TF32 0 /* tcgen05.mma kind::tf32 on the raw fp32 feature maps, fp32 accumulate in TMEM */
+#define CF_PREC_BF16 0 /* tcgen05.mma kind::f16: feature maps rounded to bf16, fp32 accumulate in TMEM          */
 #define CF_PREC_FP32 1 /* CUDA-core fp32 FMA (exact-precision mode; also serves shapes the TMA path rejects) */
-#define CF_PREC_AUTO 2 /* TF32 tensor-core path when the shape allows it, FP32 otherwise                */
+#define CF_PREC_AUTO 2 /* bf16 tensor-core path when the shape allows it, FP32 otherwise                      */
 
 /* cf_warp2d interpolation */
 #define CF_MODE_BILINEAR 0
@@ -67,9 +67,12 @@ CF_API int cf_coords_grid(float* out, int B, int H, int W, void* stream);
  * replaces `CorrBlock(fmap1, fmap2, radius=4)` (SegFlowGaussian.py:929 and 9 more call sites) =
  * torchvision raft.py:424-431 (`matmul(f1^T, f2) / sqrt(C)`) + raft.py:387-392 (3x avg_pool2d).
  * f1, f2 [B,C,H,W] fp32.  Writes all L levels into `pyramid` (cf_corr_pyramid_bytes).
- * `used_precision` (optional) receives the precision actually used (CF_PREC_TF32 / CF_PREC_FP32). */
+ * `workspace` (256-byte aligned, cf_corr_build_workspace_bytes; may be NULL when that is 0) holds the bf16
+ * copies of the feature maps for the tensor-core path.
+ * `used_precision` (optional) receives the precision actually used (CF_PREC_BF16 / CF_PREC_FP32). */
+CF_API size_t cf_corr_build_workspace_bytes(int B, int C, int H, int W, int precision);
 CF_API int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
-                  float* pyramid, int* used_precision, void* stream);
+                  float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision, void* stream);
 
 /* Rebuild levels from_level+1 .. L-1 from level from_level (F.avg_pool2d(x, 2, stride=2), floor mode). */
 CF_API int cf_corr_pool(float* pyramid, int B, int H, int W, int L, int from_level, void* stream);

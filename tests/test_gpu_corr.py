@@ -2,7 +2,7 @@
 
 Tolerances (BASELINE.json north_star): tap indices / coordinates bit-exact; fp32 lookup <= 1e-5 relative
 (max|diff| / max|ref|) -- and bit-exact against the C oracle on the same pyramid; pooling bit-exact; fp32
-correlation <= 1e-5 relative (summation order); tensor-core (TF32 in, fp32 accumulate) correlation <= 1e-2.
+correlation <= 1e-5 relative (summation order); tensor-core (bf16 in, fp32 accumulate) correlation <= 1e-2.
 """
 import numpy as np
 import pytest
@@ -159,8 +159,8 @@ def test_torchvision_call_site_adaptor():
             def build_pyramid(self, fmap1, fmap2):
                 self.blk = cf.CorrBlock(fmap1, fmap2, num_levels=4, radius=4, precision="fp32")
 
-            def index_pyramid(self, coords):
-                return self.blk(coords)
+            def index_pyramid(self, centroids_coords):
+                return self.blk(centroids_coords)
 
         model.corr_block = Adaptor()
         got = model(img1, img2, num_flow_updates=12)

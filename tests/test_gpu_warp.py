@@ -98,7 +98,8 @@ def test_full_size_properties_cfg3():
     src = torch.rand(300, 5, 224, 224, device=DEV, generator=g)
     st = cf.SpatialTransformer((224, 224)).to(DEV)
     ident = st(torch.zeros(300, 2, 224, 224, device=DEV), src)
-    assert float((ident - src).abs().max()) <= 1e-6             # zero flow = identity up to the fp32 round trip
+    # zero flow = identity up to the fp32 round trip: integer coordinates can land a few ulp(223) = 1.5e-5 off
+    assert float((ident - src).abs().max()) <= 1e-4
     flow = torch.randn(300, 2, 224, 224, device=DEV, generator=g) * 3
     other = torch.rand(300, 5, 224, 224, device=DEV, generator=g)
     lin = st(flow, 2.0 * src + other)

@@ -1,0 +1,136 @@
+"""Per-kernel timing on the GPU box (CUDA events, rotating buffers larger than L2).  Development tool:
+prints one line per kernel with its algorithmic bytes / flops and the achieved rate.
+
+    python tools/kbench.py [cfg2|cfg4|cfg3] [--reps N]
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+import cardioflow_b200 as cf  # noqa: E402
+from cardioflow_b200 import _cabi  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("cfg", nargs="?", default="cfg2")
+ap.add_argument("--reps", type=int, default=30)
+ap.add_argument("--only", default="")
+ap.add_argument("--graph", action="store_true")
+args = ap.parse_args()
+dev = torch.device("cuda:0")
+lib = _cabi.lib()
+PEAK = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
+HBM, TF = PEAK["hbm_gbs"], PEAK["bf16_tflops"]
+
+
+def timeit(fn, nrot, reps=args.reps):
+    for i in range(3):
+        fn(i % nrot)
+    torch.cuda.synchronize()
+    if args.graph:   # replay CUDA graphs: takes the Python / launch overhead out of small kernels' timings
+        graphs = []
+        for i in range(nrot):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn(i)
+            graphs.append(g)
+        eager, fn = fn, (lambda i: graphs[i].replay())
+        fn(0)
+        torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for i, (a, b) in enumerate(evs):
+        a.record()
+        fn(i % nrot)
+        b.record()
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) * 1e3 for a, b in evs)
+    return ts[len(ts) // 2], ts[0]
+
+
+def report(name, us, us_min, nbytes=None, flops=None):
+    s = f"{name:34s} median {us:9.1f} us  min {us_min:9.1f} us"
+    if nbytes:
+        gbs = nbytes / us / 1e3
+        s += f"  {nbytes / 1e6:9.1f} MB  {gbs:7.0f} GB/s = {100 * gbs / HBM:5.1f}% of measured HBM"
+    if flops:
+        tf = flops / us / 1e6
+        s += f"  {flops / 1e9:8.1f} GFLOP {tf:7.1f} TF/s = {100 * tf / TF:5.1f}% of measured bf16"
+    print(s, flush=True)
+
+
+def want(k):
+    return not args.only or k in args.only.split(",")
+
+
+if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24"):
+    P, C, H, W, IH = {"cfg2": (29, 256, 32, 32, 256), "cfg4": (64, 256, 64, 64, 512), "cfg1": (1, 256, 28, 28, 224),
+                      "ref24": (2, 256, 24, 24, 192)}[args.cfg]
+    L, R = 4, 4
+    nrot = 3 if args.cfg == "cfg2" else (2 if args.cfg == "cfg4" else 8)
+    torch.manual_seed(0)
+    f1 = [torch.randn(P, C, H, W, device=dev) for _ in range(nrot)]
+    f2 = [torch.randn(P, C, H, W, device=dev) for _ in range(nrot)]
+    pyr_bytes = lib.cf_corr_pyramid_bytes(P, H, W, L)
+    pyr = [torch.empty(pyr_bytes // 4, device=dev) for _ in range(nrot)]
+    grid = cf.coords_grid(P, H, W, device=dev)
+    coords = [grid + torch.randn(P, 2, H, W, device=dev) * 2.0 for _ in range(nrot)]
+    outs = [torch.empty(P, L * 81, H, W, device=dev) for _ in range(nrot)]
+    HWn = H * W
+    blks = {}
+    for prec in ("bf16", "fp32"):
+        if not want("build_" + prec):
+            continue
+        us, mn = timeit(lambda i: blks.__setitem__(i, cf.CorrBlock(f1[i], f2[i], precision=prec, pyramid_buffer=pyr[i])), nrot,
+                        reps=max(5, args.reps // (1 if prec == "bf16" else 4)))
+        lv = sum((H >> k) * (W >> k) for k in range(L))
+        nb = P * (2 * C * HWn * 4 + 4 * HWn * lv)
+        report(f"corr_build[{prec}] (gemm+pyramid)", us, mn, nb, 2.0 * P * HWn * HWn * C)
+    for i in range(nrot):
+        blks[i] = cf.CorrBlock(f1[i], f2[i], precision="fp32", pyramid_buffer=pyr[i])
+    from oracle.corr_oracle import lookup_algorithmic_bytes
+    lb = lookup_algorithmic_bytes(P, H, W, L, R)
+    if want("lookup"):
+        us, mn = timeit(lambda i: blks[i](coords[i], out=outs[i]), nrot)
+        report("lookup (noise coords)", us, mn, lb)
+        us, mn = timeit(lambda i: blks[i](grid, out=outs[i]), nrot)
+        report("lookup (integer grid, iter 0)", us, mn, lb)
+    if want("lookup"):
+        traj = [grid + torch.randn(P, 2, H, W, device=dev) * 0.5 * (k ** 0.5) for k in range(12)]
+        outs12 = [torch.empty(P, L * 81, H, W, device=dev) for _ in range(12)]
+
+        def twelve(i):
+            for k in range(12):
+                blks[i](traj[k], out=outs12[k])
+        us, mn = timeit(twelve, nrot, reps=max(5, args.reps // 3))
+        report("lookup x12 same pyramid (per call)", us / 12, mn / 12, lb)
+    if want("pool"):
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_pool(pyr[i].data_ptr(), P, H, W, L, 0, _cabi.stream())), nrot)
+        lv = [(H >> k) * (W >> k) for k in range(L)]
+        report("pool chain L0->L3", us, mn, P * HWn * 4 * (lv[0] + 2 * lv[1] + 2 * lv[2] + lv[3]))
+    if want("warp"):
+        for cin in (1, 5):
+            img = [torch.rand(P, cin, IH, IH, device=dev) for _ in range(nrot)]
+            flow = [torch.randn(P, 2, IH, IH, device=dev) * 3 for _ in range(nrot)]
+            wout = [torch.empty(P, cin, IH, IH, device=dev) for _ in range(nrot)]
+            us, mn = timeit(lambda i: cf.warp(img[i], flow[i], out=wout[i]), nrot)
+            report(f"warp {P}x{cin}x{IH}^2", us, mn, 4 * P * IH * IH * (2 * cin + 2))
+
+if args.cfg == "cfg3":
+    B, IH = 300, 224
+    nrot = 2
+    for cin in (1, 4, 5):
+        img = [torch.rand(B, cin, IH, IH, device=dev) for _ in range(nrot)]
+        flow = [torch.randn(B, 2, IH, IH, device=dev) * 3 for _ in range(nrot)]
+        smooth = [torch.nn.functional.interpolate(torch.randn(B, 2, 7, 7, device=dev) * 4, size=(IH, IH), mode="bicubic",
+                                                  align_corners=True).contiguous() for _ in range(nrot)]
+        wout = [torch.empty(B, cin, IH, IH, device=dev) for _ in range(nrot)]
+        us, mn = timeit(lambda i: cf.warp(img[i], flow[i], out=wout[i]), nrot)
+        report(f"warp {B}x{cin}x{IH}^2 noise flow", us, mn, 4 * B * IH * IH * (2 * cin + 2))
+        us, mn = timeit(lambda i: cf.warp(img[i], smooth[i], out=wout[i]), nrot)
+        report(f"warp {B}x{cin}x{IH}^2 smooth flow", us, mn, 4 * B * IH * IH * (2 * cin + 2))
+    lab = [torch.randint(0, 4, (B, 1, IH, IH), device=dev) for _ in range(nrot)]
+    us, mn = timeit(lambda i: cf.warp_onehot_argmax(smooth[i], lab[i]), nrot)
+    report(f"onehot-argmax {B}x{IH}^2", us, mn, B * IH * IH * 24)

@@ -32,11 +32,14 @@ constexpr int kQT = 32;  // queries per CTA
 template <int R>
 struct Geo {
     static constexpr int SIDE = 2 * R + 1;
-    static constexpr int PR = 2 * R + 4;        // window rows = logical columns: nominal 2r+2, +-1 for floor flips
-    static constexpr int QP = PR * PR + 1;      // words per query, odd
-    static constexpr int XT = SIDE * 3 * kQT;   // shared x taps: [SIDE][offset, w_lo, w_hi][query]
-    static constexpr int TR = PR * PR + kQT;   // trash words for dropped chunk components
-    static constexpr size_t SMEM = (size_t)(kQT * QP + XT + TR) * sizeof(float);
+    static constexpr int PR = 2 * R + 4;        // window rows: nominal 2r+2, +-1 for floor flips
+    static constexpr int PC = ((PR + 3 + 3) / 4) * 4;   // window columns: PR plus the alignment shift (<= 3), in 16 B chunks
+    static_assert(PC <= 16, "a window row is staged as at most 4 sixteen-byte chunks");
+    static constexpr int QP = PR * PC + 4;      // words per query: a multiple of 4 with QP / 4 odd
+    static_assert((QP / 4) % 2 == 1, "window pitch / 4 must be odd");
+    static constexpr int WIN = kQT * QP + 16;   // + the 16 B skews of win_base()
+    static constexpr int XT = SIDE * 3 * kQT;   // shared x taps: [SIDE][window column, w_lo, w_hi][query]
+    static constexpr size_t SMEM = (size_t)(WIN + XT) * sizeof(float);
 };
 
 struct LookupParams {
@@ -71,43 +74,43 @@ __device__ __forceinline__ bool nominal_taps(float c, int size) {
     return fabsf(c) <= 65536.0f && fr >= margin && fr <= 1.0f - margin;
 }
 
-// predicated read-only loads (forced predication: the staging loop must not turn into branches, so that all
-// loads of a group are in flight together)
 // The pyramid is re-read by every lookup of a CorrBlock (12x per frame pair) while each lookup streams its output
-// once: pyramid loads carry an L2 evict_last policy, output stores are streaming (st.global.cs).
+// once: pyramid reads carry an L2 evict_last policy, output stores are streaming (st.global.cs).
 __device__ __forceinline__ uint64_t l2_evict_last_policy() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
-__device__ __forceinline__ float4 ldg_f4_if(const float* p, bool pred, uint64_t pol) {
-    float4 v;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
-        "mov.b32 %0, 0;\n\tmov.b32 %1, 0;\n\tmov.b32 %2, 0;\n\tmov.b32 %3, 0;\n\t"
-        "@p ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %6;\n\t}"
-        : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-        : "l"(p), "r"((int)pred), "l"(pol));
-    return v;
+// asynchronous global -> shared copies (LDGSTS): no staging registers, every copy of a warp is in flight at once;
+// src_bytes == 0 writes zeros (zero padding outside the image)
+__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint32_t src_bytes, uint64_t pol) {
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2, %3;"
+                 ::"r"(dst), "l"(src), "r"(src_bytes), "l"(pol) : "memory");
 }
-__device__ __forceinline__ float ldg_f1_if(const float* p, bool pred, uint64_t pol) {
-    float v;
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\tmov.b32 %0, 0;\n\t"
-                 "@p ld.global.nc.L2::cache_hint.f32 %0, [%1], %3;\n\t}"
-                 : "=f"(v) : "l"(p), "r"((int)pred), "l"(pol));
-    return v;
+__device__ __forceinline__ void cp_async_4(uint32_t dst, const void* src, uint32_t src_bytes, uint64_t pol) {
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2, %3;"
+                 ::"r"(dst), "l"(src), "r"(src_bytes), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
-// Stage the (2r+4)^2 windows of the CTA's 32 queries.  A pass = one window row of 8 queries x 4 sixteen-byte
+// word offset of query q's window: pitch QP (a multiple of 4 words: 16 B-aligned chunks) plus a 16 B skew every
+// 8 queries, which makes the compute phase's scalar reads (column = per-lane shift + constant) conflict-free
+// when consecutive queries have consecutive anchors
+template <int R>
+__device__ __forceinline__ int win_base(int q) { return q * Geo<R>::QP + 4 * (q >> 3); }
+
+// Stage the (2r+4)-row windows of the CTA's 32 queries.  A pass = one window row of 8 queries x 4 sixteen-byte
 // chunks; warp w takes rows w, w+NW, ...  VEC: level width is a multiple of 4, chunks are 16 B-aligned in global
-// memory and stored shift-corrected; otherwise chunks start at the anchor column and are read element-wise.
+// memory (window column a <-> image column (ax & ~3) + a); otherwise chunks start at the anchor column and are
+// copied element-wise.
 template <int R, int NW, bool VEC>
-__device__ __forceinline__ void stage_windows(float* __restrict__ smem, const float* __restrict__ img0, int hl, int wl,
-                                              int w, int lane, int ax, int ay, unsigned flags) {
+__device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __restrict__ img0, int hl, int wl, int w,
+                                              int lane, int ax, int ay, unsigned flags) {
     using G = Geo<R>;
-    constexpr int PR = G::PR, QP = G::QP;
+    constexpr int PR = G::PR, PC = G::PC;
     constexpr int RPW = (PR + NW - 1) / NW;
-    constexpr int TRASH = kQT * QP + G::XT;   // dropped components land here (lane-private word + row offset)
     const int qq = lane >> 2, ch = lane & 3;
     const int img_words = hl * wl;
     const uint64_t pol = l2_evict_last_policy();
@@ -118,42 +121,33 @@ __device__ __forceinline__ void stage_windows(float* __restrict__ smem, const fl
         const int q_ay = __shfl_sync(0xffffffffu, ay, src);
         const unsigned q_fl = __shfl_sync(0xffffffffu, flags, src);
         const bool nomx = q_fl & 2u, nomy = q_fl & 4u;
-        const int clo = nomx ? 1 : 0, chi = nomx ? PR - 2 : PR - 1;   // logical columns the taps can read
-        const int gx = VEC ? (q_ax & ~3) + 4 * ch : q_ax + 4 * ch;  // first global column of the chunk
-        const int c0 = VEC ? 4 * ch - (q_ax & 3) : 4 * ch;           // logical column of component 0
-        const bool ch_need = !(q_fl & 1u) && (c0 + 3 >= clo) && (c0 <= chi);
-        const bool col_in = VEC ? (unsigned)gx < (unsigned)wl : true;
+        const int sh = VEC ? (q_ax & 3) : 0;
+        const int gx = q_ax - sh + 4 * ch;                             // first image column of the chunk
+        // window columns the taps can read: sh + [1, PR-2] (nominal) or sh + [0, PR-1]
+        const int clo = sh + (nomx ? 1 : 0), chi = sh + (nomx ? PR - 2 : PR - 1);
+        const bool ch_need = !(q_fl & 1u) && (4 * ch + 3 >= clo) && (4 * ch <= chi);
+        const bool col_in = (unsigned)gx < (unsigned)wl;              // VEC: chunks are entirely in or out
         const char* gq = reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)(q_ay + w) * wl + gx));
         const unsigned row_bytes = (unsigned)(NW * wl) * 4u;
-        int sidx[4];   // shared-memory word of each chunk component at this warp's first row
-#pragma unroll
-        for (int e = 0; e < 4; ++e)
-            sidx[e] = ((unsigned)(c0 + e) < (unsigned)PR ? src * QP + c0 + e : TRASH + lane) + w * PR;
-        float4 v[RPW];
-        bool wr[RPW];
+        const uint32_t sq = win_s + (uint32_t)(win_base<R>(src) + w * PC + 4 * ch) * 4u;
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
             const int r = w + NW * k;
-            const bool edge = (r == 0) || (r == PR - 1);            // rows only a flipped floor can reach
-            wr[k] = ch_need && r < PR && !(edge && nomy);
-            const bool ld = wr[k] && col_in && (unsigned)(q_ay + r) < (unsigned)hl;
-            const float* gp = reinterpret_cast<const float*>(gq + (unsigned)k * row_bytes);
-            if (VEC) {
-                v[k] = ldg_f4_if(gp, ld, pol);
-            } else {
-                v[k].x = ldg_f1_if(gp + 0, ld && (unsigned)(gx + 0) < (unsigned)wl, pol);
-                v[k].y = ldg_f1_if(gp + 1, ld && (unsigned)(gx + 1) < (unsigned)wl, pol);
-                v[k].z = ldg_f1_if(gp + 2, ld && (unsigned)(gx + 2) < (unsigned)wl, pol);
-                v[k].w = ldg_f1_if(gp + 3, ld && (unsigned)(gx + 3) < (unsigned)wl, pol);
-            }
-        }
+            const bool edge = (r == 0) || (r == PR - 1);              // rows only a flipped floor can reach
+            if (ch_need && r < PR && !(edge && nomy)) {
+                const bool row_in = (unsigned)(q_ay + r) < (unsigned)hl;
+                const char* gp = gq + (unsigned)k * row_bytes;
+                const uint32_t d = sq + (uint32_t)(NW * k * PC) * 4u;
+                if (VEC) {
+                    const bool in = row_in && col_in;
+                    cp_async_16(d, in ? gp : reinterpret_cast<const char*>(img0), in ? 16u : 0u, pol);
+                } else {
 #pragma unroll
-        for (int k = 0; k < RPW; ++k) {
-            if (wr[k]) {
-                smem[sidx[0] + NW * k * PR] = v[k].x;
-                smem[sidx[1] + NW * k * PR] = v[k].y;
-                smem[sidx[2] + NW * k * PR] = v[k].z;
-                smem[sidx[3] + NW * k * PR] = v[k].w;
+                    for (int e = 0; e < 4; ++e) {
+                        const bool in = row_in && (unsigned)(gx + e) < (unsigned)wl;
+                        cp_async_4(d + 4u * e, in ? gp + 4 * e : reinterpret_cast<const char*>(img0), in ? 4u : 0u, pol);
+                    }
+                }
             }
         }
     }
@@ -162,11 +156,11 @@ __device__ __forceinline__ void stage_windows(float* __restrict__ smem, const fl
 template <int R, int NW>
 __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__ LookupParams P) {
     using G = Geo<R>;
-    constexpr int SIDE = G::SIDE, PR = G::PR, QP = G::QP;
+    constexpr int SIDE = G::SIDE, PR = G::PR, PC = G::PC;
     constexpr int JPW = (SIDE + NW - 1) / NW;   // output rows (and taps per axis) per warp
-    extern __shared__ float smem[];
-    float* const win = smem;                    // [kQT][QP]
-    float* const xt = smem + kQT * QP;          // [SIDE][3][kQT]
+    extern __shared__ __align__(16) float smem[];
+    float* const win = smem;                    // windows: win_base(q) + row * PC + column
+    float* const xt = smem + G::WIN;            // [SIDE][3][kQT]: x taps (window column, w_lo, w_hi)
 
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const unsigned task = blockIdx.x / (unsigned)P.L;
@@ -175,6 +169,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     const unsigned n = n0 + lane;
     const bool valid = n < (unsigned)P.N;
     const int hl = P.lh[l], wl = P.lw[l];
+    const bool vec = (wl & 3) == 0;
 
     // ---- per-lane query (every warp holds the same 32 queries) ----
     unsigned b = 0, p = 0;
@@ -192,11 +187,21 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     // window anchor: nominal first tap minus one (the round trip can move a floor by +-1)
     const int ax = dead ? 0 : __float2int_rd(cx) - R - 1;
     const int ay = dead ? 0 : __float2int_rd(cy) - R - 1;
+    const int sh = vec ? (ax & 3) : 0;             // window column of the anchor
     const bool nom_x = dead || nominal_taps<R>(cx, wl);
     const bool nom_y = dead || nominal_taps<R>(cy, hl);
     const bool fast = __all_sync(0xffffffffu, nom_x && nom_y);
 
-    // ---- taps: warp w computes taps w*JPW.. of both axes; x taps are shared, y taps stay in registers ----
+    // ---- start the window copies, then compute the taps while they are in flight ----
+    {
+        const float* __restrict__ img0 = P.level[l] + (size_t)n0 * hl * wl;
+        const unsigned flags = (dead ? 1u : 0u) | (nom_x ? 2u : 0u) | (nom_y ? 4u : 0u);
+        const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
+        if (vec) stage_windows<R, NW, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
+        else stage_windows<R, NW, false>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
+    }
+
+    // taps: warp w computes taps w*JPW.. of both axes; x taps are shared, y taps stay in registers
     int yoff[JPW];
     float ywl[JPW], ywh[JPW];
     {
@@ -209,22 +214,15 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                 int i0;
                 float lo, hi;
                 axis_tap(cx, t - R, s1x, i0, lo, hi);
-                xt[(t * 3 + 0) * kQT + lane] = __int_as_float(min(max(i0 - ax, 0), PR - 2));
+                xt[(t * 3 + 0) * kQT + lane] = __int_as_float(min(max(i0 - ax, 0), PR - 2) + sh);
                 xt[(t * 3 + 1) * kQT + lane] = lo;
                 xt[(t * 3 + 2) * kQT + lane] = hi;
                 axis_tap(cy, t - R, s1y, i0, ywl[k], ywh[k]);
-                yoff[k] = min(max(i0 - ay, 0), PR - 2) * PR;
+                yoff[k] = min(max(i0 - ay, 0), PR - 2) * PC;
             }
         }
     }
-
-    // ---- stage the windows ----
-    {
-        const float* __restrict__ img0 = P.level[l] + (size_t)n0 * hl * wl;
-        const unsigned flags = (dead ? 1u : 0u) | (nom_x ? 2u : 0u) | (nom_y ? 4u : 0u);
-        if ((wl & 3) == 0) stage_windows<R, NW, true>(smem, img0, hl, wl, w, lane, ax, ay, flags);
-        else stage_windows<R, NW, false>(smem, img0, hl, wl, w, lane, ax, ay, flags);
-    }
+    cp_async_wait_all();
     __syncthreads();
 
     // ---- (2r+1) x JPW outputs per lane, channel-major stores (128 B per warp per channel) ----
@@ -233,47 +231,41 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     const unsigned HW = (unsigned)P.HW;
     const int j0 = w * JPW;
     float* __restrict__ o = P.out + ((size_t)b * P.L * K + (size_t)l * K + j0) * HW + p;
-    const float* sq = win + lane * QP;
+    const size_t ostep = (size_t)SIDE * HW;    // next x tap = SIDE channels further
+    const float* sq = win + win_base<R>(lane);
     if (dead) {
 #pragma unroll
-        for (int k = 0; k < JPW; ++k)
-            if (j0 + k < SIDE)
+        for (int i = 0; i < SIDE; ++i, o += ostep)
 #pragma unroll
-                for (int i = 0; i < SIDE; ++i) __stcs(o + (i * SIDE + k) * HW, 0.0f);
+            for (int k = 0; k < JPW; ++k)
+                if (j0 + k < SIDE) __stcs(o + k * HW, 0.0f);
         return;
     }
     if (fast) {
-        // nominal taps: x tap i reads logical columns i+1, i+2; output row j reads window rows j+1, j+2
-        float xl[SIDE], xh[SIDE];
+        // nominal taps: x tap i reads window columns sh+i+1, sh+i+2; output row j reads window rows j+1, j+2
+        const float* rp = sq + (j0 + 1) * PC + sh + 1;
+        float r[JPW + 1][SIDE + 1];
 #pragma unroll
-        for (int i = 0; i < SIDE; ++i) {
-            xl[i] = xt[(i * 3 + 1) * kQT + lane];
-            xh[i] = xt[(i * 3 + 2) * kQT + lane];
-        }
-        const float* rp = sq + (j0 + 1) * PR + 1;
-        float ra[SIDE + 1], rb[SIDE + 1];
+        for (int k = 0; k <= JPW; ++k)
 #pragma unroll
-        for (int c = 0; c <= SIDE; ++c) ra[c] = rp[c];
+            for (int c = 0; c <= SIDE; ++c) r[k][c] = (j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f;
 #pragma unroll
-        for (int k = 0; k < JPW; ++k) {
-            if (j0 + k < SIDE) {
+        for (int i = 0; i < SIDE; ++i, o += ostep) {
+            const float xl = xt[(i * 3 + 1) * kQT + lane], xh = xt[(i * 3 + 2) * kQT + lane];
 #pragma unroll
-                for (int c = 0; c <= SIDE; ++c) rb[c] = rp[(k + 1) * PR + c];
-#pragma unroll
-                for (int i = 0; i < SIDE; ++i) {
-                    float acc = __fmul_rn(ra[i], __fmul_rn(xl[i], ywl[k]));
-                    acc = fmaf(ra[i + 1], __fmul_rn(xh[i], ywl[k]), acc);
-                    acc = fmaf(rb[i], __fmul_rn(xl[i], ywh[k]), acc);
-                    acc = fmaf(rb[i + 1], __fmul_rn(xh[i], ywh[k]), acc);
-                    __stcs(o + (i * SIDE + k) * HW, acc);
+            for (int k = 0; k < JPW; ++k) {
+                if (j0 + k < SIDE) {
+                    float acc = __fmul_rn(r[k][i], __fmul_rn(xl, ywl[k]));
+                    acc = fmaf(r[k][i + 1], __fmul_rn(xh, ywl[k]), acc);
+                    acc = fmaf(r[k + 1][i], __fmul_rn(xl, ywh[k]), acc);
+                    acc = fmaf(r[k + 1][i + 1], __fmul_rn(xh, ywh[k]), acc);
+                    __stcs(o + k * HW, acc);
                 }
-#pragma unroll
-                for (int c = 0; c <= SIDE; ++c) ra[c] = rb[c];
             }
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < SIDE; ++i) {
+        for (int i = 0; i < SIDE; ++i, o += ostep) {
             const int xo = __float_as_int(xt[(i * 3 + 0) * kQT + lane]);
             const float xl = xt[(i * 3 + 1) * kQT + lane], xh = xt[(i * 3 + 2) * kQT + lane];
 #pragma unroll
@@ -282,9 +274,9 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                     const float* t = sq + yoff[k] + xo;
                     float acc = __fmul_rn(t[0], __fmul_rn(xl, ywl[k]));
                     acc = fmaf(t[1], __fmul_rn(xh, ywl[k]), acc);
-                    acc = fmaf(t[PR], __fmul_rn(xl, ywh[k]), acc);
-                    acc = fmaf(t[PR + 1], __fmul_rn(xh, ywh[k]), acc);
-                    __stcs(o + (i * SIDE + k) * HW, acc);
+                    acc = fmaf(t[PC], __fmul_rn(xl, ywh[k]), acc);
+                    acc = fmaf(t[PC + 1], __fmul_rn(xh, ywh[k]), acc);
+                    __stcs(o + k * HW, acc);
                 }
             }
         }

@@ -21,6 +21,14 @@ ap.add_argument("--only", default="")
 ap.add_argument("--graph", action="store_true")
 args = ap.parse_args()
 dev = torch.device("cuda:0")
+if os.environ.get("KB_L2_FETCH"):
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    torch.zeros(1, device=dev)
+    print("cudaDeviceSetLimit(MaxL2FetchGranularity) ->", rt.cudaDeviceSetLimit(5, ctypes.c_size_t(int(os.environ["KB_L2_FETCH"]))))
+    v = ctypes.c_size_t()
+    rt.cudaDeviceGetLimit(ctypes.byref(v), 5)
+    print("L2 fetch granularity now", v.value)
 lib = _cabi.lib()
 PEAK = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
 HBM, TF = PEAK["hbm_gbs"], PEAK["bf16_tflops"]

@@ -136,7 +136,7 @@ class CorrBlock:
     frame pairs reuse device memory (the reference allocates afresh every call).  Errors follow torchvision raft.py:368-383 (ValueError).
     """
 
-    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None, pyramid_buffer=None):
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None, pyramid_buffer=None, on_the_fly=False):
         if fmap1.shape != fmap2.shape:
             raise ValueError(f"Input feature maps should have the same shape, instead got {tuple(fmap1.shape)} "
                              f"(fmap1.shape) != {tuple(fmap2.shape)} (fmap2.shape)")
@@ -154,6 +154,25 @@ class CorrBlock:
         self.radius = radius
         B, _, H, W = fmap1.shape
         self._meta = (B, H, W, num_levels, radius)
+        self.on_the_fly = bool(on_the_fly)
+        if self.on_the_fly:
+            # K4: keep fmap1 and the pooled fmap2 pyramid, recompute window correlations per lookup (fp32;
+            # forward only -- the training graph goes through the materialised path)
+            if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+                raise NotImplementedError("on_the_fly=True is a forward-only path; use it under torch.no_grad()")
+            lib = _cabi.lib()
+            C = fmap1.shape[1]
+            self._f1 = _cabi.f32c(fmap1)
+            f2 = _cabi.f32c(fmap2)
+            self._f2_pyramid = torch.empty(lib.cf_fmap_pyramid_bytes(B, C, H, W, num_levels) // 4, dtype=torch.float32,
+                                           device=f2.device)
+            with torch.cuda.device(f2.device):
+                _cabi.check(lib.cf_fmap_pyramid_build(f2.data_ptr(), B, C, H, W, num_levels,
+                                                      self._f2_pyramid.data_ptr(), _cabi.stream()), "cf_fmap_pyramid_build")
+            self.used_precision = "fp32"
+            self._pyramid = None
+            self.corr_pyramid = None
+            return
         self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer)
         self.used_precision = {0: "bf16", 1: "fp32"}.get(getattr(_CorrBuild, "last_used_precision", -1), "?")
         self.corr_pyramid = _level_views(self._pyramid, B, H, W, num_levels)
@@ -171,6 +190,7 @@ class CorrBlock:
         lib = _cabi.lib()
         packed = torch.zeros(lib.cf_corr_pyramid_bytes(B, H, W, L) // 4, dtype=torch.float32, device=lvl0.device)
         self.num_levels, self.radius = L, radius
+        self.on_the_fly = False
         self._meta = (B, H, W, L, radius)
         self._pyramid = packed
         self.used_precision = "external"
@@ -183,8 +203,25 @@ class CorrBlock:
         B, H, W, _, _ = self._meta
         if tuple(coords.shape) != (B, 2, H, W):
             raise ValueError(f"coords must be [{B}, 2, {H}, {W}], got {tuple(coords.shape)}")
+        if self.on_the_fly:
+            return self._lookup_on_the_fly(coords, out)
         _cabi.require_cuda(self._pyramid, coords)
         return _CorrLookup.apply(self._pyramid, coords, self._meta, out)
+
+    def _lookup_on_the_fly(self, coords, out=None):
+        B, H, W, L, r = self._meta
+        _cabi.require_cuda(self._f1, coords)
+        c = _cabi.f32c(coords)
+        shape = (B, L * (2 * r + 1) ** 2, H, W)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float32, device=c.device)
+        elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous fp32 tensor of shape {shape}")
+        with torch.cuda.device(c.device):
+            _cabi.check(_cabi.lib().cf_corr_lookup_fused(self._f1.data_ptr(), self._f2_pyramid.data_ptr(), c.data_ptr(),
+                                                         B, self._f1.shape[1], H, W, L, r, out.data_ptr(),
+                                                         _cabi.stream()), "cf_corr_lookup_fused")
+        return out
 
     # torchvision-style aliases, so the same object can stand in for raft_large().corr_block's methods
     index_pyramid = __call__

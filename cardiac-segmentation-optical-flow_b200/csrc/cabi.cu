@@ -178,4 +178,86 @@ int cf_warp2d_onehot_argmax(const float* flow, const int64_t* label, int num_cla
     return launch_warp2d_onehot_argmax(flow, label, num_classes, B, H, W, out, (cudaStream_t)stream);
 }
 
+// ---- on-the-fly lookup (K4) --------------------------------------------------------------------------------
+size_t cf_fmap_pyramid_level_offset(int B, int C, int H, int W, int level) {
+    LevelDims d;
+    if (B < 1 || C < 1 || level < 0 || level > CF_MAX_LEVELS || !fmap_level_dims(B, C, H, W, level, &d)) return 0;
+    return d.off[level];
+}
+
+size_t cf_fmap_pyramid_bytes(int B, int C, int H, int W, int L) { return cf_fmap_pyramid_level_offset(B, C, H, W, L); }
+
+int cf_fmap_pyramid_build(const float* f2, int B, int C, int H, int W, int L, float* f2_pyramid, void* stream) {
+    CF_REQUIRE(f2 && f2_pyramid, CF_ERR_BAD_ARG, "cf_fmap_pyramid_build: null pointer");
+    CF_REQUIRE(C > 0, CF_ERR_BAD_ARG, "cf_fmap_pyramid_build: C must be positive");
+    CF_REQUIRE(((uintptr_t)f2_pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_fmap_pyramid_build: f2_pyramid must be 256-byte aligned");
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    return launch_fmap_pyramid(f2, B, C, H, W, L, f2_pyramid, (cudaStream_t)stream);
+}
+
+int cf_corr_lookup_fused(const float* f1, const float* f2_pyramid, const float* coords, int B, int C, int H, int W,
+                         int L, int r, float* out, void* stream) {
+    CF_REQUIRE(f1 && f2_pyramid && coords && out, CF_ERR_BAD_ARG, "cf_corr_lookup_fused: null pointer");
+    CF_REQUIRE(C > 0, CF_ERR_BAD_ARG, "cf_corr_lookup_fused: C must be positive");
+    CF_REQUIRE(r >= 1 && r <= CF_MAX_RADIUS, CF_ERR_UNSUPPORTED, "cf_corr_lookup_fused: radius %d not in [1,%d]", r, CF_MAX_RADIUS);
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    return launch_lookup_fused(f1, f2_pyramid, coords, B, C, H, W, L, r, out, (cudaStream_t)stream);
+}
+
+// ---- 8(f) rows: backward passes, VecInt, point sampling -------------------------------------------------------
+int cf_warp2d_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W,
+                  float* grad_src, float* grad_flow, void* stream) {
+    CF_REQUIRE(flow && src && grad_out, CF_ERR_BAD_ARG, "cf_warp2d_bwd: null pointer");
+    CF_REQUIRE(grad_src || grad_flow, CF_ERR_BAD_ARG, "cf_warp2d_bwd: neither grad_src nor grad_flow requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_warp2d_bwd: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    return launch_warp2d_bwd(flow, src, grad_out, B, C, H, W, grad_src, grad_flow, (cudaStream_t)stream);
+}
+
+int cf_corr_lookup_bwd(const float* coords, const float* grad_out, int B, int H, int W, int L, int r,
+                       float* grad_pyramid, void* stream) {
+    CF_REQUIRE(coords && grad_out && grad_pyramid, CF_ERR_BAD_ARG, "cf_corr_lookup_bwd: null pointer");
+    CF_REQUIRE(r >= 1 && r <= CF_MAX_RADIUS, CF_ERR_UNSUPPORTED, "cf_corr_lookup_bwd: radius %d not in [1,%d]", r, CF_MAX_RADIUS);
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    return launch_lookup_bwd(d, coords, grad_out, B, H, W, L, r, grad_pyramid, (cudaStream_t)stream);
+}
+
+int cf_corr_pool_bwd(float* grad_pyramid, int B, int H, int W, int L, void* stream) {
+    CF_REQUIRE(grad_pyramid, CF_ERR_BAD_ARG, "cf_corr_pool_bwd: null pointer");
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    return launch_pool_chain_bwd(grad_pyramid, d, (long)B * H * W, L, (cudaStream_t)stream);
+}
+
+int cf_corr_volume_bwd(const float* f1, const float* f2, const float* grad_corr, int B, int C, int H, int W,
+                       float* grad_f1, float* grad_f2, void* stream) {
+    CF_REQUIRE(f1 && f2 && grad_corr, CF_ERR_BAD_ARG, "cf_corr_volume_bwd: null pointer");
+    CF_REQUIRE(grad_f1 || grad_f2, CF_ERR_BAD_ARG, "cf_corr_volume_bwd: neither grad_f1 nor grad_f2 requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_corr_volume_bwd: bad shape");
+    return launch_corr_volume_bwd(f1, f2, grad_corr, B, C, H * W, grad_f1, grad_f2, (cudaStream_t)stream);
+}
+
+int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream) {
+    CF_REQUIRE(vec && out, CF_ERR_BAD_ARG, "cf_vecint: null pointer");
+    CF_REQUIRE(B > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_vecint: bad shape B=%d H=%d W=%d", B, H, W);
+    CF_REQUIRE(nsteps >= 0 && nsteps <= 30, CF_ERR_BAD_ARG, "cf_vecint: nsteps %d not in [0,30]", nsteps);
+    CF_REQUIRE(nsteps < 2 || work, CF_ERR_BAD_ARG, "cf_vecint: work buffer required for nsteps >= 2");
+    CF_REQUIRE(out != vec && work != vec && (work != out || nsteps < 2), CF_ERR_BAD_ARG, "cf_vecint: buffers must not alias");
+    return launch_vecint(vec, B, H, W, nsteps, out, work, (cudaStream_t)stream);
+}
+
+int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int size_h, int size_w,
+                     int mode, float* out, void* stream) {
+    CF_REQUIRE(locs && src && out, CF_ERR_BAD_ARG, "cf_sample_points: null pointer");
+    CF_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1 && P > 0 && size_h > 1 && size_w > 1, CF_ERR_BAD_ARG, "cf_sample_points: bad shape");
+    CF_REQUIRE(mode == CF_MODE_BILINEAR || mode == CF_MODE_NEAREST, CF_ERR_UNSUPPORTED, "cf_sample_points: mode %d", mode);
+    return launch_sample_points(locs, src, B, C, H, W, P, size_h, size_w, mode, out, (cudaStream_t)stream);
+}
+
 }  // extern "C"

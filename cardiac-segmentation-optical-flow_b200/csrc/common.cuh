@@ -73,9 +73,10 @@ int launch_warp2d_onehot_argmax(const float* flow, const int64_t* label, int ncl
 int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W,
                       float* gsrc, float* gflow, cudaStream_t s);
 int launch_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, cudaStream_t s);
-int launch_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int mode,
-                         float* out, cudaStream_t s);
+int launch_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int SH, int SW,
+                         int mode, float* out, cudaStream_t s);
 
+int launch_pool2x2(const float* in, float* out, long n_img, int h, int w, cudaStream_t s);
 int launch_pool_chain(float* pyramid, const LevelDims& d, long n_img, int L, int from_level, cudaStream_t s);
 int launch_pool_chain_bwd(float* gpyr, const LevelDims& d, long n_img, int L, cudaStream_t s);
 
@@ -96,6 +97,8 @@ int launch_lookup_taps(const LevelDims& d, const float* coords, int B, int H, in
 int launch_lookup_bwd(const LevelDims& d, const float* coords, const float* go, int B, int H, int W, int L,
                       int r, float* gpyr, cudaStream_t s);
 
+// pooled-fmap2 pyramid of the on-the-fly lookup: level l = [B, C, h_l, w_l], 256-byte aligned offsets
+bool fmap_level_dims(int B, int C, int H, int W, int L, LevelDims* d);
 int launch_fmap_pyramid(const float* f2, int B, int C, int H, int W, int L, float* f2pyr, cudaStream_t s);
 int launch_lookup_fused(const float* f1, const float* f2pyr, const float* coords, int B, int C, int H, int W,
                         int L, int r, float* out, cudaStream_t s);

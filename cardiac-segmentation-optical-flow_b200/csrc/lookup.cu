@@ -23,6 +23,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "sampling.cuh"
 
 namespace cf {
 namespace {
@@ -54,15 +55,6 @@ struct LookupParams {
     int HW;
     int L;
 };
-
-// one axis tap: sampling coordinate -> floor index, weight of tap i0 and of tap i0 + 1
-__device__ __forceinline__ void axis_tap(float c, int d, float s1, int& i0, float& w_lo, float& w_hi) {
-    const float u = lookup_coord(__fadd_rn(c, (float)d), s1);
-    const float f = floorf(u);
-    i0 = __float2int_rd(u);
-    w_hi = __fsub_rn(u, f);
-    w_lo = __fsub_rn(__fadd_rn(f, 1.0f), u);
-}
 
 // The round trip moves a coordinate p = c + k (|k| <= r) by less than 2^-24 * (4|p| + S) (four roundings of
 // magnitude <= |p| resp. S/2).  If frac(c) keeps twice that margin from both integers, floor(u_k) == floor(c) + k

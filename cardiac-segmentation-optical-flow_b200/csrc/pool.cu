@@ -46,20 +46,24 @@ __global__ void __launch_bounds__(256) pool2x2_kernel(const float* __restrict__ 
 
 }  // namespace
 
+int launch_pool2x2(const float* in, float* out, long n_img, int h, int w, cudaStream_t s) {
+    if (w % 4 == 0 && aligned16(in) && ((reinterpret_cast<uintptr_t>(out) & 7u) == 0)) {
+        const long total = n_img * (h / 2) * (w / 4);
+        pool2x2_vec_kernel<<<cdiv(total, 256), 256, 0, s>>>(in, out, h, w, total);
+    } else {
+        const long total = n_img * (h / 2) * (w / 2);
+        pool2x2_kernel<<<cdiv(total, 256), 256, 0, s>>>(in, out, h, w, total);
+    }
+    CF_CHECK_LAUNCH("pool2x2_kernel");
+    return CF_OK;
+}
+
 int launch_pool_chain(float* pyramid, const LevelDims& d, long n_img, int L, int from_level, cudaStream_t s) {
     char* base = reinterpret_cast<char*>(pyramid);
     for (int l = from_level; l + 1 < L; ++l) {
-        const float* in = reinterpret_cast<const float*>(base + d.off[l]);
-        float* out = reinterpret_cast<float*>(base + d.off[l + 1]);
-        const int h = d.h[l], w = d.w[l];
-        if (w % 4 == 0) {
-            const long total = n_img * (h / 2) * (w / 4);
-            pool2x2_vec_kernel<<<cdiv(total, 256), 256, 0, s>>>(in, out, h, w, total);
-        } else {
-            const long total = n_img * (h / 2) * (w / 2);
-            pool2x2_kernel<<<cdiv(total, 256), 256, 0, s>>>(in, out, h, w, total);
-        }
-        CF_CHECK_LAUNCH("pool2x2_kernel");
+        const int rc = launch_pool2x2(reinterpret_cast<const float*>(base + d.off[l]),
+                                      reinterpret_cast<float*>(base + d.off[l + 1]), n_img, d.h[l], d.w[l], s);
+        if (rc) return rc;
     }
     return CF_OK;
 }

@@ -5,40 +5,10 @@
 // compulsory traffic on the coordinate tensor).  Here: one launch, flow read once (128-bit), all C channels
 // sampled per pixel from the taps computed once, 128-bit stores.  HBM-bound: 4*H*W*(2C+2) bytes per item.
 #include "common.cuh"
+#include "sampling.cuh"
 
 namespace cf {
 namespace {
-
-struct Tap {
-    int x0, y0;
-    float w00, w01, w10, w11;  // nw, ne, sw, se (ATen order)
-};
-
-__device__ __forceinline__ Tap make_tap(float uy, float ux) {
-    Tap t;
-    const float fx = floorf(ux), fy = floorf(uy);
-    t.x0 = __float2int_rd(ux);
-    t.y0 = __float2int_rd(uy);
-    const float wxh = __fsub_rn(ux, fx), wxl = __fsub_rn(__fadd_rn(fx, 1.0f), ux);
-    const float wyh = __fsub_rn(uy, fy), wyl = __fsub_rn(__fadd_rn(fy, 1.0f), uy);
-    t.w00 = __fmul_rn(wxl, wyl);
-    t.w01 = __fmul_rn(wxh, wyl);
-    t.w10 = __fmul_rn(wxl, wyh);
-    t.w11 = __fmul_rn(wxh, wyh);
-    return t;
-}
-
-__device__ __forceinline__ float fetch(const float* __restrict__ img, int H, int W, int y, int x) {
-    return ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) ? __ldg(img + (size_t)y * W + x) : 0.0f;
-}
-
-__device__ __forceinline__ float sample_bilinear(const float* __restrict__ img, int H, int W, const Tap& t) {
-    float acc = __fmul_rn(fetch(img, H, W, t.y0, t.x0), t.w00);
-    acc = fmaf(fetch(img, H, W, t.y0, t.x0 + 1), t.w01, acc);
-    acc = fmaf(fetch(img, H, W, t.y0 + 1, t.x0), t.w10, acc);
-    acc = fmaf(fetch(img, H, W, t.y0 + 1, t.x0 + 1), t.w11, acc);
-    return acc;
-}
 
 template <int VEC, int MODE>
 __global__ void __launch_bounds__(256) warp2d_kernel(const float* __restrict__ flow, const float* __restrict__ src,

@@ -133,7 +133,7 @@ class SpatialTransformerContour(nn.Module):
         out = torch.empty(B, C, locs.shape[2], locs.shape[3], dtype=torch.float32, device=src.device)
         with torch.cuda.device(src.device):
             _cabi.check(_cabi.lib().cf_sample_points(locs.data_ptr(), src.data_ptr(), B, C, H, W, P,
-                                                     _MODES[self.mode], out.data_ptr(), _cabi.stream()),
+                                                     self.shape[-2], self.shape[-1], _MODES[self.mode], out.data_ptr(), _cabi.stream()),
                         "cf_sample_points")
         # reference side effect (integration.py:23-24): the argument ends up normalised to [-1, 1]
         with torch.no_grad():

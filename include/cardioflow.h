@@ -131,9 +131,11 @@ CF_API int cf_corr_volume_bwd(const float* f1, const float* f2, const float* gra
 CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream);
 
 /* SpatialTransformerContour (integration.py:5-34): sample src [B,C,H,W] at P points; locs [B,2,P] with
- * ch0 = x, ch1 = y (the reference's un-swapped order); out [B,C,P]. */
-CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int mode,
-                     float* out, void* stream);
+ * ch0 = x, ch1 = y (the reference's un-swapped order), in pixels of a (size_h, size_w) transformer: the reference
+ * normalises channel i by `self.shape[~i] - 1` (x by size_w - 1, y by size_h - 1) and grid_sample un-normalises
+ * with the image's own (H, W); out [B,C,P]. */
+CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int size_h,
+                     int size_w, int mode, float* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -318,26 +318,53 @@ def main():
         h2d = sum(v.numel() * v.element_size() for v in host.values())
         d2h = h_outs.numel() * 4 + h_warp.numel() * 4
 
-        def e2e_step():
-            d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        # Two-deep pipeline: the H2D copies of step i+1 run on a copy stream (PCIe is full duplex) while step i
+        # computes and streams its results back; every step still moves all of its inputs and outputs.
+        copy_stream = torch.cuda.Stream(device=dev)
+        main_stream = torch.cuda.current_stream(dev)
+        dbuf = [{k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in host.items()} for _ in range(2)]
+        in_ready = [torch.cuda.Event() for _ in range(2)]
+        in_free = [torch.cuda.Event() for _ in range(2)]
+
+        def upload(i):
+            s = i % 2
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(in_free[s])           # the step that last read this buffer set is done
+                for k, v in host.items():
+                    dbuf[s][k].copy_(v, non_blocking=True)
+                in_ready[s].record(copy_stream)
+
+        def e2e_step(i, prefetch=True):
+            s = i % 2
+            if prefetch:
+                upload(i + 1)
+            main_stream.wait_event(in_ready[s])
+            d = dbuf[s]
             b = cf.CorrBlock(d["f1"], d["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
                              pyramid_buffer=pyramid)
             for k in range(ITERS):
                 b(d["coords"][k], out=outs[k])
                 h_outs[k].copy_(outs[k], non_blocking=True)
             w = st(flow=d["flow"], original=d["img"])
+            in_free[s].record(main_stream)
             h_warp.copy_(w, non_blocking=True)
 
-        for _ in range(2):
-            e2e_step()
+        for ev in in_free:
+            ev.record(main_stream)
+        upload(0)
+        e2e_step(0)
+        e2e_step(1, prefetch=False)
         torch.cuda.synchronize()
         if dist:
             dist.barrier()
+        # the timed region contains exactly e2e_steps uploads and e2e_steps downloads
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(e2e_steps):
-            e2e_step()
+        upload(2)
+        for i in range(2, 2 + e2e_steps):
+            e2e_step(i, prefetch=(i + 1 < 2 + e2e_steps))
         e1.record()
+        copy_stream.synchronize()
         torch.cuda.synchronize()
         e2e_ms = e0.elapsed_time(e1)
 

@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
         cx = __fmul_rn(__ldg(P.coords + (b * 2 + 0) * P.HW + p), inv);
         cy = __fmul_rn(__ldg(P.coords + (b * 2 + 1) * P.HW + p), inv);
     }
-    const bool dead = !valid || !(fabsf(cx) < 1.0e6f) || !(fabsf(cy) < 1.0e6f);
+    const bool dead = !valid || !(fabsf(cx) < kDeadCoord) || !(fabsf(cy) < kDeadCoord);
     const int ax = dead ? 0 : __float2int_rd(cx) - R - 1;
     const int ay = dead ? 0 : __float2int_rd(cy) - R - 1;
     anchor[lane][0] = dead ? (1 << 30) : ax;   // far outside any image: nothing is written back
@@ -67,10 +67,11 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
         int xo[SIDE];
         float xl[SIDE], xh[SIDE];
         const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
+        const float rcx = __frcp_rn(s1x), rcy = __frcp_rn(s1y);   // IEEE-rounded reciprocals for div_small
 #pragma unroll
         for (int i = 0; i < SIDE; ++i) {
             int i0;
-            axis_tap(cx, i - R, s1x, i0, xl[i], xh[i]);
+            axis_tap(cx, i - R, s1x, rcx, i0, xl[i], xh[i]);
             xo[i] = i0 - ax;   // in [0, PR-2] by the round-trip bound (lookup.cu: nominal_taps)
         }
         const float* g = P.go + ((size_t)b * P.L * K + (size_t)l * K) * P.HW + p;
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
         for (int j = 0; j < SIDE; ++j) {
             int j0;
             float yl, yh;
-            axis_tap(cy, j - R, s1y, j0, yl, yh);
+            axis_tap(cy, j - R, s1y, rcy, j0, yl, yh);
             float* rowp = my + min(max(j0 - ay, 0), PR - 2) * PR;
 #pragma unroll
             for (int i = 0; i < SIDE; ++i) {

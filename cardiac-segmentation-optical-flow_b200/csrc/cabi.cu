@@ -38,6 +38,7 @@ bool corr_level_dims(int B, int H, int W, int L, LevelDims* d) {
 namespace {
 int check_corr_shape(int B, int H, int W, int L, LevelDims* d) {
     CF_REQUIRE(B > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "B, H, W must be positive (got %d, %d, %d)", B, H, W);
+    CF_REQUIRE(H <= 4096 && W <= 4096, CF_ERR_UNSUPPORTED, "feature maps larger than 4096 are not supported (got %dx%d)", H, W);
     CF_REQUIRE(L >= 1 && L <= CF_MAX_LEVELS, CF_ERR_UNSUPPORTED, "num_levels %d not in [1,%d]", L, CF_MAX_LEVELS);
     // torchvision raft.py:368-383: the coarsest level must keep at least 2 values per axis
     const int min_size = 2 << (L - 1);

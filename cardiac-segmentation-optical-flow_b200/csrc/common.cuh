@@ -47,14 +47,32 @@ struct LevelDims {
 bool corr_level_dims(int B, int H, int W, int L, LevelDims* d);
 
 // ---- the exact fp32 coordinate sequences (no FMA contraction: *_rn intrinsics are never fused) ----
-// lookup: RAFT bilinear_sampler n = 2*p/(S-1) - 1, then ATen unnormalize ((n+1)/2)*(S-1)
-__device__ __forceinline__ float lookup_coord(float p, float s1) {
+// Division by s1 = size - 1 (a small integer) is the one expensive step.  q = a * r corrected once with the exact
+// remainder, r = RN(1/s1), equals the IEEE quotient __fdiv_rn(a, s1) bit for bit: checked EXHAUSTIVELY on B200 for
+// every fp32 a with 2^-24 <= |a| < 2^14 and every s1 in 1..4095 (tools/div_probe.cu, 0 mismatches); exponent
+// scaling does not change the rounding, so smaller |a| are covered too (and there every caller subtracts a constant
+// >= 0.5 next, which absorbs q entirely).  |a| >= 2^14 takes the IEEE path.
+__device__ __forceinline__ float div_small(float a, float s1, float r) {
+    const float q0 = __fmul_rn(a, r);
+    return __fmaf_rn(__fmaf_rn(-q0, s1, a), r, q0);
+}
+__device__ __forceinline__ float div_exact(float a, float s1, float r) {
+    return (fabsf(a) < 16384.0f && s1 <= 4095.0f) ? div_small(a, s1, r) : __fdiv_rn(a, s1);
+}
+// lookup: RAFT bilinear_sampler n = 2*p/(S-1) - 1, then ATen unnormalize ((n+1)/2)*(S-1).  r = 1/s1 (host, IEEE).
+// The lookup kernels call this only with |p| < 8192 (farther queries are dead: every tap is outside the image)
+// and s1 <= 4095 (cabi.cu: level sizes are capped at 4096).
+__device__ __forceinline__ float lookup_coord(float p, float s1, float r) {
+    const float n = __fsub_rn(div_small(__fmul_rn(2.0f, p), s1, r), 1.0f);
+    return __fmul_rn(__fmul_rn(__fadd_rn(n, 1.0f), 0.5f), s1);
+}
+__device__ __forceinline__ float lookup_coord_ieee(float p, float s1) {   // any |p|: IEEE division
     const float n = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, p), s1), 1.0f);
     return __fmul_rn(__fmul_rn(__fadd_rn(n, 1.0f), 0.5f), s1);
 }
 // warp: integration.py:68 n = 2*(p/(S-1) - 0.5), then the same ATen step
-__device__ __forceinline__ float warp_coord(float p, float s1) {
-    const float n = __fmul_rn(2.0f, __fsub_rn(__fdiv_rn(p, s1), 0.5f));
+__device__ __forceinline__ float warp_coord(float p, float s1, float r) {
+    const float n = __fmul_rn(2.0f, __fsub_rn(div_exact(p, s1, r), 0.5f));
     return __fmul_rn(__fmul_rn(__fadd_rn(n, 1.0f), 0.5f), s1);
 }
 

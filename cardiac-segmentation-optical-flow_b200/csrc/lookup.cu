@@ -9,13 +9,15 @@
 //   * every tap coordinate goes through the reference's exact fp32 sequence (normalise -> un-normalise, no
 //     FMA contraction), so tap indices / weights are bit-exact.  The 2*(2r+1) per-axis taps of a query are
 //     computed ONCE per CTA (split over the warps) and the x taps are shared through shared memory
-//   * the (2r+4)^2 window each query can touch is staged into shared memory with 128-bit read-only loads:
-//     a warp pass covers 8 queries x 4 sixteen-byte chunks of ONE window row (8 distinct 128 B lines per
-//     request instead of 32), stored shift-corrected so that all queries see the same logical column ->
-//     bank = f(query) only: conflict-free loads in the compute phase (query pitch is odd); out-of-image
-//     positions are stored as zeros, so zero padding costs nothing in the inner loop
+//   * the (2r+3)^2 window each query can touch (anchored by the side on which its floors can flip) is staged into
+//     shared memory with asynchronous 16-byte copies (cp.async / LDGSTS, L2 evict_last): a warp pass covers 8
+//     queries x 4 chunks of ONE window row (8 distinct 128 B lines per request instead of 32); out-of-image
+//     chunks are zero-filled by the copy itself, so zero padding costs nothing in the inner loop; the tap
+//     arithmetic runs while the copies are in flight
+//   * the division by (size - 1) in the coordinate round trip is an exact reciprocal-multiply-correct sequence
+//     (common.cuh: div_small, bit-identical to IEEE division, verified exhaustively on B200)
 //   * warp w evaluates the window rows j = w*JPW .. of the (2r+1)^2 outputs from shared memory in ATen's
-//     nw, ne, sw, se order.  When no lane of the warp sits within 2^-8 of an integer coordinate (where the
+//     nw, ne, sw, se order.  When no lane of the warp sits within ~1e-5 of an integer coordinate (where the
 //     round trip can flip a floor) the taps are provably the nominal ones and a register-window fast path
 //     with static indexing runs; otherwise the general path with per-lane offsets
 //   * outputs go straight into the final [B, L*K, H, W] layout: for a fixed channel the 32 lanes write 128
@@ -30,16 +32,19 @@ namespace {
 
 constexpr int kQT = 32;  // queries per CTA
 
+// Window geometry.  The round trip moves a coordinate by far less than 0.5, so the floors of a query's taps can only
+// flip DOWN when frac(c) < 0.5 and only UP otherwise: anchoring the window at floor(c) - r - (frac < 0.5) makes
+// 2r+3 rows / columns enough for every case (nominal taps: 2r+2).
 template <int R>
 struct Geo {
     static constexpr int SIDE = 2 * R + 1;
-    static constexpr int PR = 2 * R + 4;        // window rows: nominal 2r+2, +-1 for floor flips
-    static constexpr int PC = ((PR + 3 + 3) / 4) * 4;   // window columns: PR plus the alignment shift (<= 3), in 16 B chunks
+    static constexpr int PR = 2 * R + 3;                 // window rows / logical columns
+    static constexpr int PC = ((PR + 3 + 3) / 4) * 4;    // stored columns: PR plus the alignment shift (<= 3), in 16 B chunks
     static_assert(PC <= 16, "a window row is staged as at most 4 sixteen-byte chunks");
-    static constexpr int QP = PR * PC + 4;      // words per query: a multiple of 4 with QP / 4 odd
-    static_assert((QP / 4) % 2 == 1, "window pitch / 4 must be odd");
-    static constexpr int WIN = kQT * QP + 16;   // + the 16 B skews of win_base()
-    static constexpr int XT = SIDE * 3 * kQT;   // shared x taps: [SIDE][window column, w_lo, w_hi][query]
+    static constexpr int QP = PR * PC + (((PR * PC / 4) % 2 == 0) ? 4 : 0);   // words per query: QP / 4 odd
+    static_assert(QP % 4 == 0 && (QP / 4) % 2 == 1, "window pitch / 4 must be odd");
+    static constexpr int WIN = kQT * QP + 16;            // + the 16 B skews of win_base()
+    static constexpr int XT = SIDE * 3 * kQT;            // shared x taps: [SIDE][window column, w_lo, w_hi][query]
     static constexpr size_t SMEM = (size_t)(WIN + XT) * sizeof(float);
 };
 
@@ -47,6 +52,8 @@ struct LookupParams {
     const float* level[CF_MAX_LEVELS];
     int lh[CF_MAX_LEVELS];
     int lw[CF_MAX_LEVELS];
+    float rcp_h[CF_MAX_LEVELS];   // 1 / (h_l - 1), 1 / (w_l - 1): IEEE-rounded on the host (div_small)
+    float rcp_w[CF_MAX_LEVELS];
     const float* coords;
     float* out;
     float* taps;    // taps kernel only
@@ -54,16 +61,21 @@ struct LookupParams {
     long N;         // B*H*W
     int HW;
     int L;
+    int lshift;     // log2(L) when L is a power of two, else -1
 };
+
+// flags a lane publishes about its query (shuffled to the lanes that stage its window)
+constexpr unsigned kDead = 1u, kNomX = 2u, kNomY = 4u, kLoX = 8u, kLoY = 16u;
 
 // The round trip moves a coordinate p = c + k (|k| <= r) by less than 2^-24 * (4|p| + S) (four roundings of
 // magnitude <= |p| resp. S/2).  If frac(c) keeps twice that margin from both integers, floor(u_k) == floor(c) + k
-// for every tap: the nominal window, no flipped floors.
+// for every tap: the nominal window, no flipped floors.  `lo` = frac(c) < 0.5 (floors can only flip down).
 template <int R>
-__device__ __forceinline__ bool nominal_taps(float c, int size) {
+__device__ __forceinline__ void classify(float c, int size, bool& nominal, bool& lo) {
     const float fr = __fsub_rn(c, floorf(c));
     const float margin = fmaf(4.0f, fabsf(c) + (float)(R + 1), (float)size) * 1.1920929e-7f;   // 2 * bound
-    return fabsf(c) <= 65536.0f && fr >= margin && fr <= 1.0f - margin;
+    nominal = fr >= margin && fr <= 1.0f - margin;
+    lo = fr < 0.5f;
 }
 
 // The pyramid is re-read by every lookup of a CorrBlock (12x per frame pair) while each lookup streams its output
@@ -93,10 +105,9 @@ __device__ __forceinline__ void cp_async_wait_all() {
 template <int R>
 __device__ __forceinline__ int win_base(int q) { return q * Geo<R>::QP + 4 * (q >> 3); }
 
-// Stage the (2r+4)-row windows of the CTA's 32 queries.  A pass = one window row of 8 queries x 4 sixteen-byte
-// chunks; warp w takes rows w, w+NW, ...  VEC: level width is a multiple of 4, chunks are 16 B-aligned in global
-// memory (window column a <-> image column (ax & ~3) + a); otherwise chunks start at the anchor column and are
-// copied element-wise.
+// Stage the windows of the CTA's 32 queries.  A pass = one window row of 8 queries x 4 sixteen-byte chunks; warp w
+// takes rows w, w+NW, ...  VEC: level width is a multiple of 4, chunks are 16 B-aligned in global memory (window
+// column a <-> image column (ax & ~3) + a); otherwise chunks start at the anchor column and are copied element-wise.
 template <int R, int NW, bool VEC>
 __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __restrict__ img0, int hl, int wl, int w,
                                               int lane, int ax, int ay, unsigned flags) {
@@ -112,12 +123,14 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
         const int q_ax = __shfl_sync(0xffffffffu, ax, src);
         const int q_ay = __shfl_sync(0xffffffffu, ay, src);
         const unsigned q_fl = __shfl_sync(0xffffffffu, flags, src);
-        const bool nomx = q_fl & 2u, nomy = q_fl & 4u;
         const int sh = VEC ? (q_ax & 3) : 0;
         const int gx = q_ax - sh + 4 * ch;                             // first image column of the chunk
-        // window columns the taps can read: sh + [1, PR-2] (nominal) or sh + [0, PR-1]
-        const int clo = sh + (nomx ? 1 : 0), chi = sh + (nomx ? PR - 2 : PR - 1);
-        const bool ch_need = !(q_fl & 1u) && (4 * ch + 3 >= clo) && (4 * ch <= chi);
+        // window columns the taps can read: nominal = the 2r+2 columns from (lo ? 1 : 0), else all PR
+        const int c0 = (q_fl & kNomX) ? ((q_fl & kLoX) ? 1 : 0) : 0;
+        const int c1 = (q_fl & kNomX) ? c0 + 2 * R + 1 : PR - 1;
+        const bool ch_need = !(q_fl & kDead) && (4 * ch + 3 >= sh + c0) && (4 * ch <= sh + c1) && (4 * ch < PC);
+        // the one row only a flipped floor can reach
+        const int skip = (q_fl & kNomY) ? ((q_fl & kLoY) ? 0 : PR - 1) : -1;
         const bool col_in = (unsigned)gx < (unsigned)wl;              // VEC: chunks are entirely in or out
         const char* gq = reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)(q_ay + w) * wl + gx));
         const unsigned row_bytes = (unsigned)(NW * wl) * 4u;
@@ -125,19 +138,18 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
             const int r = w + NW * k;
-            const bool edge = (r == 0) || (r == PR - 1);              // rows only a flipped floor can reach
-            if (ch_need && r < PR && !(edge && nomy)) {
+            if (ch_need && r < PR && r != skip) {
                 const bool row_in = (unsigned)(q_ay + r) < (unsigned)hl;
                 const char* gp = gq + (unsigned)k * row_bytes;
                 const uint32_t d = sq + (uint32_t)(NW * k * PC) * 4u;
                 if (VEC) {
                     const bool in = row_in && col_in;
-                    cp_async_16(d, in ? gp : reinterpret_cast<const char*>(img0), in ? 16u : 0u, pol);
+                    cp_async_16(d, gp, in ? 16u : 0u, pol);   // src-size 0: nothing is read, 16 zero bytes are written
                 } else {
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const bool in = row_in && (unsigned)(gx + e) < (unsigned)wl;
-                        cp_async_4(d + 4u * e, in ? gp + 4 * e : reinterpret_cast<const char*>(img0), in ? 4u : 0u, pol);
+                        cp_async_4(d + 4u * e, gp + 4 * e, in ? 4u : 0u, pol);
                     }
                 }
             }
@@ -155,39 +167,41 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     float* const xt = smem + G::WIN;            // [SIDE][3][kQT]: x taps (window column, w_lo, w_hi)
 
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const unsigned task = blockIdx.x / (unsigned)P.L;
+    // levels interleave in launch order (read-heavy fine levels next to store-heavy coarse ones)
+    const unsigned task = P.lshift >= 0 ? (blockIdx.x >> P.lshift) : blockIdx.x / (unsigned)P.L;
     const int l = (int)(blockIdx.x - task * (unsigned)P.L);
-    const unsigned n0 = task * kQT;
-    const unsigned n = n0 + lane;
-    const bool valid = n < (unsigned)P.N;
+    const unsigned n0 = task * kQT;             // CTA-uniform
+    const bool valid = n0 + lane < (unsigned)P.N;
     const int hl = P.lh[l], wl = P.lw[l];
     const bool vec = (wl & 3) == 0;
 
-    // ---- per-lane query (every warp holds the same 32 queries) ----
-    unsigned b = 0, p = 0;
+    // ---- per-lane query (every warp holds the same 32 queries); batch index from CTA-uniform arithmetic ----
+    unsigned b = n0 / (unsigned)P.HW;
+    unsigned p = n0 - b * (unsigned)P.HW + lane;
+    if (p >= (unsigned)P.HW) { p -= (unsigned)P.HW; ++b; }      // H*W >= 256 > 32: at most one wrap
     float cx = 0.0f, cy = 0.0f;
     if (valid) {
-        b = n / (unsigned)P.HW;
-        p = n - b * (unsigned)P.HW;
-        const float inv = 1.0f / (float)(1 << l);   // division by 2^l == multiplication by 2^-l, exactly
+        const float inv = __int_as_float((127 - l) << 23);      // 2^-l: the reference's division by 2^l, exactly
         const float* cp = P.coords + (size_t)b * 2 * P.HW + p;
         cx = __fmul_rn(__ldg(cp), inv);
         cy = __fmul_rn(__ldg(cp + P.HW), inv);
     }
     // every tap of a query this far out is outside any image -> zeros (also catches NaN / inf)
-    const bool dead = !valid || !(fabsf(cx) < 1.0e6f) || !(fabsf(cy) < 1.0e6f);
-    // window anchor: nominal first tap minus one (the round trip can move a floor by +-1)
-    const int ax = dead ? 0 : __float2int_rd(cx) - R - 1;
-    const int ay = dead ? 0 : __float2int_rd(cy) - R - 1;
-    const int sh = vec ? (ax & 3) : 0;             // window column of the anchor
-    const bool nom_x = dead || nominal_taps<R>(cx, wl);
-    const bool nom_y = dead || nominal_taps<R>(cy, hl);
-    const bool fast = __all_sync(0xffffffffu, nom_x && nom_y);
+    const bool dead = !valid || !(fabsf(cx) < kDeadCoord) || !(fabsf(cy) < kDeadCoord);
+    bool nom_x, nom_y, lo_x, lo_y;
+    classify<R>(cx, wl, nom_x, lo_x);
+    classify<R>(cy, hl, nom_y, lo_y);
+    // window anchor: first nominal tap, minus one when floors can flip down
+    const int ax = dead ? 0 : __float2int_rd(cx) - R - (lo_x ? 1 : 0);
+    const int ay = dead ? 0 : __float2int_rd(cy) - R - (lo_y ? 1 : 0);
+    const int sh = vec ? (ax & 3) : 0;             // stored column of the anchor
+    const bool fast = __all_sync(0xffffffffu, dead || (nom_x && nom_y));
 
     // ---- start the window copies, then compute the taps while they are in flight ----
     {
         const float* __restrict__ img0 = P.level[l] + (size_t)n0 * hl * wl;
-        const unsigned flags = (dead ? 1u : 0u) | (nom_x ? 2u : 0u) | (nom_y ? 4u : 0u);
+        const unsigned flags = (dead ? kDead : 0u) | (nom_x ? kNomX : 0u) | (nom_y ? kNomY : 0u) | (lo_x ? kLoX : 0u) |
+                               (lo_y ? kLoY : 0u);
         const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
         if (vec) stage_windows<R, NW, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
         else stage_windows<R, NW, false>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
@@ -198,6 +212,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     float ywl[JPW], ywh[JPW];
     {
         const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
+        const float rx = P.rcp_w[l], ry = P.rcp_h[l];
 #pragma unroll
         for (int k = 0; k < JPW; ++k) {
             const int t = w * JPW + k;
@@ -205,11 +220,11 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
             if (t < SIDE) {
                 int i0;
                 float lo, hi;
-                axis_tap(cx, t - R, s1x, i0, lo, hi);
+                axis_tap(cx, t - R, s1x, rx, i0, lo, hi);
                 xt[(t * 3 + 0) * kQT + lane] = __int_as_float(min(max(i0 - ax, 0), PR - 2) + sh);
                 xt[(t * 3 + 1) * kQT + lane] = lo;
                 xt[(t * 3 + 2) * kQT + lane] = hi;
-                axis_tap(cy, t - R, s1y, i0, ywl[k], ywh[k]);
+                axis_tap(cy, t - R, s1y, ry, i0, ywl[k], ywh[k]);
                 yoff[k] = min(max(i0 - ay, 0), PR - 2) * PC;
             }
         }
@@ -222,27 +237,29 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     constexpr int K = SIDE * SIDE;
     const unsigned HW = (unsigned)P.HW;
     const int j0 = w * JPW;
-    float* __restrict__ o = P.out + ((size_t)b * P.L * K + (size_t)l * K + j0) * HW + p;
-    const size_t ostep = (size_t)SIDE * HW;    // next x tap = SIDE channels further
+    float* ok[JPW];                               // one store pointer per output row, advanced by SIDE channels per x tap
+#pragma unroll
+    for (int k = 0; k < JPW; ++k) ok[k] = P.out + ((size_t)b * P.L * K + (size_t)l * K + j0 + k) * HW + p;
+    const size_t ostep = (size_t)SIDE * HW;
     const float* sq = win + win_base<R>(lane);
     if (dead) {
 #pragma unroll
-        for (int i = 0; i < SIDE; ++i, o += ostep)
+        for (int i = 0; i < SIDE; ++i)
 #pragma unroll
             for (int k = 0; k < JPW; ++k)
-                if (j0 + k < SIDE) __stcs(o + k * HW, 0.0f);
+                if (j0 + k < SIDE) { __stcs(ok[k], 0.0f); ok[k] += ostep; }
         return;
     }
     if (fast) {
-        // nominal taps: x tap i reads window columns sh+i+1, sh+i+2; output row j reads window rows j+1, j+2
-        const float* rp = sq + (j0 + 1) * PC + sh + 1;
+        // nominal taps: with o = (lo ? 1 : 0), x tap i reads stored columns sh+o+i, +1; output row j reads rows o+j, +1
+        const float* rp = sq + (j0 + (lo_y ? 1 : 0)) * PC + sh + (lo_x ? 1 : 0);
         float r[JPW + 1][SIDE + 1];
 #pragma unroll
         for (int k = 0; k <= JPW; ++k)
 #pragma unroll
             for (int c = 0; c <= SIDE; ++c) r[k][c] = (j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f;
 #pragma unroll
-        for (int i = 0; i < SIDE; ++i, o += ostep) {
+        for (int i = 0; i < SIDE; ++i) {
             const float xl = xt[(i * 3 + 1) * kQT + lane], xh = xt[(i * 3 + 2) * kQT + lane];
 #pragma unroll
             for (int k = 0; k < JPW; ++k) {
@@ -251,13 +268,14 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                     acc = fmaf(r[k][i + 1], __fmul_rn(xh, ywl[k]), acc);
                     acc = fmaf(r[k + 1][i], __fmul_rn(xl, ywh[k]), acc);
                     acc = fmaf(r[k + 1][i + 1], __fmul_rn(xh, ywh[k]), acc);
-                    __stcs(o + k * HW, acc);
+                    __stcs(ok[k], acc);
+                    ok[k] += ostep;
                 }
             }
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < SIDE; ++i, o += ostep) {
+        for (int i = 0; i < SIDE; ++i) {
             const int xo = __float_as_int(xt[(i * 3 + 0) * kQT + lane]);
             const float xl = xt[(i * 3 + 1) * kQT + lane], xh = xt[(i * 3 + 2) * kQT + lane];
 #pragma unroll
@@ -268,7 +286,8 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                     acc = fmaf(t[1], __fmul_rn(xh, ywl[k]), acc);
                     acc = fmaf(t[PC], __fmul_rn(xl, ywh[k]), acc);
                     acc = fmaf(t[PC + 1], __fmul_rn(xh, ywh[k]), acc);
-                    __stcs(o + k * HW, acc);
+                    __stcs(ok[k], acc);
+                    ok[k] += ostep;
                 }
             }
         }
@@ -287,11 +306,14 @@ __global__ void __launch_bounds__(128) lookup_taps_kernel(const __grid_constant_
     const float cx = __fdiv_rn(__ldg(P.coords + (b * 2 + 0) * P.HW + p), sc);
     const float cy = __fdiv_rn(__ldg(P.coords + (b * 2 + 1) * P.HW + p), sc);
     const float s1x = (float)(P.lw[l] - 1), s1y = (float)(P.lh[l] - 1);
+    const float rx = P.rcp_w[l], ry = P.rcp_h[l];
+    const bool far = !(fabsf(cx) < kDeadCoord) || !(fabsf(cy) < kDeadCoord);   // outside div_small's checked range
     const size_t base = (((size_t)l * P.N + n) * 2) * G::SIDE;
 #pragma unroll
     for (int i = 0; i < G::SIDE; ++i) {
-        const float ux = lookup_coord(__fadd_rn(cx, (float)(i - R)), s1x);
-        const float uy = lookup_coord(__fadd_rn(cy, (float)(i - R)), s1y);
+        const float px = __fadd_rn(cx, (float)(i - R)), py = __fadd_rn(cy, (float)(i - R));
+        const float ux = far ? lookup_coord_ieee(px, s1x) : lookup_coord(px, s1x, rx);
+        const float uy = far ? lookup_coord_ieee(py, s1y) : lookup_coord(py, s1y, ry);
         P.taps[base + i] = ux;
         P.taps[base + G::SIDE + i] = uy;
         P.idx[base + i] = __float2int_rd(ux);
@@ -300,8 +322,8 @@ __global__ void __launch_bounds__(128) lookup_taps_kernel(const __grid_constant_
 }
 
 template <int R, int NW>
-int launch_lookup_rw(const LookupParams& P, long grid, cudaStream_t s) {
-    lookup_kernel<R, NW><<<(unsigned)grid, 32 * NW, Geo<R>::SMEM, s>>>(P);
+int launch_lookup_rw(const LookupParams& P, long ngroups, cudaStream_t s) {
+    lookup_kernel<R, NW><<<(unsigned)(ngroups * P.L), 32 * NW, Geo<R>::SMEM, s>>>(P);
     CF_CHECK_LAUNCH("lookup_kernel");
     return CF_OK;
 }
@@ -309,13 +331,12 @@ int launch_lookup_rw(const LookupParams& P, long grid, cudaStream_t s) {
 template <int R>
 int launch_lookup_r(const LookupParams& P, cudaStream_t s) {
     const long ngroups = (P.N + kQT - 1) / kQT;
-    const long grid = ngroups * P.L;
-    if (P.N > 0x7fffffffL || grid > 0x7fffffffL) return fail(CF_ERR_UNSUPPORTED, "lookup grid too large (%ld tasks)", grid);
+    if (P.N > 0x7fffffffL || ngroups * P.L > 0x7fffffffL) return fail(CF_ERR_UNSUPPORTED, "lookup grid too large (%ld queries)", P.N);
     static const int nw = [] { const char* e = getenv("CF_LOOKUP_NW"); return e ? atoi(e) : 3; }();   // tuning knob
     switch (nw) {
-        case 2: return launch_lookup_rw<R, 2>(P, grid, s);
-        case 4: return launch_lookup_rw<R, 4>(P, grid, s);
-        default: return launch_lookup_rw<R, 3>(P, grid, s);
+        case 2: return launch_lookup_rw<R, 2>(P, ngroups, s);
+        case 4: return launch_lookup_rw<R, 4>(P, ngroups, s);
+        default: return launch_lookup_rw<R, 3>(P, ngroups, s);
     }
 }
 
@@ -333,11 +354,16 @@ LookupParams make_params(const float* pyramid, const LevelDims& d, const float* 
         P.level[l] = pyramid ? reinterpret_cast<const float*>(reinterpret_cast<const char*>(pyramid) + d.off[l]) : nullptr;
         P.lh[l] = d.h[l];
         P.lw[l] = d.w[l];
+        P.rcp_h[l] = 1.0f / (float)(d.h[l] - 1);
+        P.rcp_w[l] = 1.0f / (float)(d.w[l] - 1);
     }
     P.coords = coords;
     P.N = (long)B * H * W;
     P.HW = H * W;
     P.L = L;
+    P.lshift = -1;
+    for (int k = 0; k < 4; ++k)
+        if ((1 << k) == L) P.lshift = k;
     return P;
 }
 

@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(32 * kNWF) lookup_fused_kernel(const __grid_co
         cx = __fmul_rn(__ldg(P.coords + (b * 2 + 0) * P.HW + p), inv);
         cy = __fmul_rn(__ldg(P.coords + (b * 2 + 1) * P.HW + p), inv);
     }
-    const bool dead = !valid || !(fabsf(cx) < 1.0e6f) || !(fabsf(cy) < 1.0e6f);
+    const bool dead = !valid || !(fabsf(cx) < kDeadCoord) || !(fabsf(cy) < kDeadCoord);
     const int ax = dead ? 0 : __float2int_rd(cx) - R - 1;
     const int ay = dead ? 0 : __float2int_rd(cy) - R - 1;
 
@@ -144,6 +144,7 @@ __global__ void __launch_bounds__(32 * kNWF) lookup_fused_kernel(const __grid_co
     float* o = P.out + ((size_t)b * P.L * K + (size_t)l * K) * HW + p;
     const float* sq = win + lane * PITCH;
     const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
+        const float rcx = __frcp_rn(s1x), rcy = __frcp_rn(s1y);   // IEEE-rounded reciprocals for div_small
     int yo[JPW];
     float yl[JPW], yh[JPW];
 #pragma unroll
@@ -151,14 +152,14 @@ __global__ void __launch_bounds__(32 * kNWF) lookup_fused_kernel(const __grid_co
         const int j = w * JPW + k;
         int j0 = 0;
         yl[k] = yh[k] = 0.0f;
-        if (j < SIDE) axis_tap(cy, j - R, s1y, j0, yl[k], yh[k]);
+        if (j < SIDE) axis_tap(cy, j - R, s1y, rcy, j0, yl[k], yh[k]);
         yo[k] = min(max(j0 - ay, 0), PR - 2) * PR;
     }
 #pragma unroll
     for (int i = 0; i < SIDE; ++i) {
         int i0;
         float xl, xh;
-        axis_tap(cx, i - R, s1x, i0, xl, xh);
+        axis_tap(cx, i - R, s1x, rcx, i0, xl, xh);
         const int xo = min(max(i0 - ax, 0), PR - 2);
 #pragma unroll
         for (int k = 0; k < JPW; ++k) {

@@ -37,12 +37,16 @@ __device__ __forceinline__ float sample_bilinear(const float* __restrict__ img, 
 }
 
 // one axis tap: sampling coordinate -> floor index, weight of tap i0 and of tap i0 + 1
-__device__ __forceinline__ void axis_tap(float c, int d, float s1, int& i0, float& w_lo, float& w_hi) {
-    const float u = lookup_coord(__fadd_rn(c, (float)d), s1);
+__device__ __forceinline__ void axis_tap(float c, int d, float s1, float rcp, int& i0, float& w_lo, float& w_hi) {
+    const float u = lookup_coord(__fadd_rn(c, (float)d), s1, rcp);
     const float f = floorf(u);
     i0 = __float2int_rd(u);
     w_hi = __fsub_rn(u, f);
     w_lo = __fsub_rn(__fadd_rn(f, 1.0f), u);
 }
+
+// Queries this far out have every tap outside any level image (sizes <= 4096): zeros.  Also catches NaN / inf and
+// keeps |2 * (c + d)| < 2^14 for div_small.
+constexpr float kDeadCoord = 8000.0f;
 
 }  // namespace cf

@@ -12,7 +12,8 @@ namespace {
 
 template <int VEC, int MODE>
 __global__ void __launch_bounds__(256) warp2d_kernel(const float* __restrict__ flow, const float* __restrict__ src,
-                                                     float* __restrict__ out, int C, int H, int W, long total) {
+                                                     float* __restrict__ out, int C, int H, int W, float ry, float rx,
+                                                     long total) {
     const long t = (long)blockIdx.x * 256 + threadIdx.x;
     if (t >= total) return;
     const int wv = W / VEC;
@@ -39,8 +40,8 @@ __global__ void __launch_bounds__(256) warp2d_kernel(const float* __restrict__ f
     int ny[VEC], nx[VEC];
 #pragma unroll
     for (int v = 0; v < VEC; ++v) {
-        const float uy = warp_coord(__fadd_rn((float)y, dy[v]), s1y);
-        const float ux = warp_coord(__fadd_rn((float)(x + v), dx[v]), s1x);
+        const float uy = warp_coord(__fadd_rn((float)y, dy[v]), s1y, ry);
+        const float ux = warp_coord(__fadd_rn((float)(x + v), dx[v]), s1x, rx);
         if (MODE == CF_MODE_BILINEAR) {
             tap[v] = make_tap(uy, ux);
         } else {  // ATen nearest: nearbyint = round half to even
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(256) warp2d_kernel(const float* __restrict__ f
 }
 
 __global__ void __launch_bounds__(256) warp2d_taps_kernel(const float* __restrict__ flow, float* __restrict__ taps,
-                                                          int H, int W, long total) {
+                                                          int H, int W, float ry, float rx, long total) {
     const long t = (long)blockIdx.x * 256 + threadIdx.x;
     if (t >= total) return;
     const int x = (int)(t % W);
@@ -74,8 +75,8 @@ __global__ void __launch_bounds__(256) warp2d_taps_kernel(const float* __restric
     const long b = row / H;
     const size_t HW = (size_t)H * W, pix = (size_t)y * W + x;
     const float dy = flow[(b * 2 + 0) * HW + pix], dx = flow[(b * 2 + 1) * HW + pix];
-    taps[(b * 2 + 0) * HW + pix] = warp_coord(__fadd_rn((float)y, dy), (float)(H - 1));
-    taps[(b * 2 + 1) * HW + pix] = warp_coord(__fadd_rn((float)x, dx), (float)(W - 1));
+    taps[(b * 2 + 0) * HW + pix] = warp_coord(__fadd_rn((float)y, dy), (float)(H - 1), ry);
+    taps[(b * 2 + 1) * HW + pix] = warp_coord(__fadd_rn((float)x, dx), (float)(W - 1), rx);
 }
 
 // a6: argmax_c warp(one_hot(label))[c] without materialising the one-hot tensor.  The per-class value is
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(256) warp2d_taps_kernel(const float* __restric
 __global__ void __launch_bounds__(256) warp2d_onehot_argmax_kernel(const float* __restrict__ flow,
                                                                     const int64_t* __restrict__ label,
                                                                     int64_t* __restrict__ out, int ncls, int H, int W,
-                                                                    long total) {
+                                                                    float ry, float rx, long total) {
     const long t = (long)blockIdx.x * 256 + threadIdx.x;
     if (t >= total) return;
     const int x = (int)(t % W);
@@ -91,8 +92,8 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_kernel(const float* 
     const int y = (int)(row % H);
     const long b = row / H;
     const size_t HW = (size_t)H * W, pix = (size_t)y * W + x;
-    const float uy = warp_coord(__fadd_rn((float)y, __ldg(flow + (b * 2 + 0) * HW + pix)), (float)(H - 1));
-    const float ux = warp_coord(__fadd_rn((float)x, __ldg(flow + (b * 2 + 1) * HW + pix)), (float)(W - 1));
+    const float uy = warp_coord(__fadd_rn((float)y, __ldg(flow + (b * 2 + 0) * HW + pix)), (float)(H - 1), ry);
+    const float ux = warp_coord(__fadd_rn((float)x, __ldg(flow + (b * 2 + 1) * HW + pix)), (float)(W - 1), rx);
     const Tap tp = make_tap(uy, ux);
     const float w[4] = {tp.w00, tp.w01, tp.w10, tp.w11};
     const int ty[4] = {tp.y0, tp.y0, tp.y0 + 1, tp.y0 + 1};
@@ -142,12 +143,13 @@ int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int 
     const bool vec = (W % 4 == 0) && aligned16(flow) && aligned16(src) && aligned16(out);
     const long total = (long)B * H * (vec ? W / 4 : W);
     const int grid = cdiv(total, 256);
+    const float ry = 1.0f / (float)(H - 1), rx = 1.0f / (float)(W - 1);   // IEEE-rounded reciprocals for div_small
     if (mode == CF_MODE_BILINEAR) {
-        if (vec) warp2d_kernel<4, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, total);
-        else warp2d_kernel<1, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, total);
+        if (vec) warp2d_kernel<4, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
+        else warp2d_kernel<1, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
     } else {
-        if (vec) warp2d_kernel<4, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, total);
-        else warp2d_kernel<1, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, total);
+        if (vec) warp2d_kernel<4, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
+        else warp2d_kernel<1, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
     }
     CF_CHECK_LAUNCH("warp2d_kernel");
     return CF_OK;
@@ -155,7 +157,7 @@ int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int 
 
 int launch_warp2d_taps(const float* flow, int B, int H, int W, float* taps, cudaStream_t s) {
     const long total = (long)B * H * W;
-    warp2d_taps_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, taps, H, W, total);
+    warp2d_taps_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, taps, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
     CF_CHECK_LAUNCH("warp2d_taps_kernel");
     return CF_OK;
 }
@@ -163,7 +165,7 @@ int launch_warp2d_taps(const float* flow, int B, int H, int W, float* taps, cuda
 int launch_warp2d_onehot_argmax(const float* flow, const int64_t* label, int ncls, int B, int H, int W,
                                 int64_t* out, cudaStream_t s) {
     const long total = (long)B * H * W;
-    warp2d_onehot_argmax_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, label, out, ncls, H, W, total);
+    warp2d_onehot_argmax_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, label, out, ncls, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
     CF_CHECK_LAUNCH("warp2d_onehot_argmax_kernel");
     return CF_OK;
 }

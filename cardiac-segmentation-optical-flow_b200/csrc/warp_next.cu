@@ -19,7 +19,8 @@ namespace {
 // may sample the same source texel), d(out)/d(flow) is a per-pixel reduction over channels (no atomics).
 __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict__ flow, const float* __restrict__ src,
                                                          const float* __restrict__ go, float* __restrict__ gsrc,
-                                                         float* __restrict__ gflow, int C, int H, int W, long total) {
+                                                         float* __restrict__ gflow, int C, int H, int W, float ry, float rx,
+                                                         long total) {
     const long t = (long)blockIdx.x * 256 + threadIdx.x;
     if (t >= total) return;
     const int x = (int)(t % W);
@@ -28,8 +29,8 @@ __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict
     const long b = row / H;
     const size_t HW = (size_t)H * W, pix = (size_t)y * W + x;
     const float s1y = (float)(H - 1), s1x = (float)(W - 1);
-    const float uy = warp_coord(__fadd_rn((float)y, __ldg(flow + (b * 2 + 0) * HW + pix)), s1y);
-    const float ux = warp_coord(__fadd_rn((float)x, __ldg(flow + (b * 2 + 1) * HW + pix)), s1x);
+    const float uy = warp_coord(__fadd_rn((float)y, __ldg(flow + (b * 2 + 0) * HW + pix)), s1y, ry);
+    const float ux = warp_coord(__fadd_rn((float)x, __ldg(flow + (b * 2 + 1) * HW + pix)), s1x, rx);
     const Tap tp = make_tap(uy, ux);
     const float fx = floorf(ux), fy = floorf(uy);
     // ATen names: (ix_nw, iy_nw) = (fx, fy); se = nw + 1
@@ -75,7 +76,7 @@ __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict
 // ---------------------------------------------------------------------------------------------- VecInt
 // out = s*v + warp(s*v, flow = s*v), s a power of two (exact), both channels per thread.
 __global__ void __launch_bounds__(256) vecint_step_kernel(const float* __restrict__ v, float* __restrict__ out,
-                                                          float s, int H, int W, long total) {
+                                                          float s, int H, int W, float ry, float rx, long total) {
     const long t = (long)blockIdx.x * 256 + threadIdx.x;
     if (t >= total) return;
     const int x = (int)(t % W);
@@ -86,8 +87,8 @@ __global__ void __launch_bounds__(256) vecint_step_kernel(const float* __restric
     const float* v0 = v + (b * 2 + 0) * HW;
     const float* v1 = v + (b * 2 + 1) * HW;
     const float dy = __fmul_rn(__ldg(v0 + pix), s), dx = __fmul_rn(__ldg(v1 + pix), s);
-    const float uy = warp_coord(__fadd_rn((float)y, dy), (float)(H - 1));
-    const float ux = warp_coord(__fadd_rn((float)x, dx), (float)(W - 1));
+    const float uy = warp_coord(__fadd_rn((float)y, dy), (float)(H - 1), ry);
+    const float ux = warp_coord(__fadd_rn((float)x, dx), (float)(W - 1), rx);
     const Tap tp = make_tap(uy, ux);
     const bool y0in = (unsigned)tp.y0 < (unsigned)H, y1in = (unsigned)(tp.y0 + 1) < (unsigned)H;
     const bool x0in = (unsigned)tp.x0 < (unsigned)W, x1in = (unsigned)(tp.x0 + 1) < (unsigned)W;
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(128) sample_points_kernel(const float* __restr
 int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W, float* gsrc,
                       float* gflow, cudaStream_t s) {
     const long total = (long)B * H * W;
-    warp2d_bwd_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, src, go, gsrc, gflow, C, H, W, total);
+    warp2d_bwd_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, src, go, gsrc, gflow, C, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
     CF_CHECK_LAUNCH("warp2d_bwd_kernel");
     return CF_OK;
 }
@@ -170,7 +171,7 @@ int launch_vecint(const float* vec, int B, int H, int W, int nsteps, float* out,
     const float* cur = vec;
     for (int k = 0; k < nsteps; ++k) {
         float* dst = ((nsteps - 1 - k) % 2 == 0) ? out : work;
-        vecint_step_kernel<<<cdiv(total, 256), 256, 0, s>>>(cur, dst, k == 0 ? scale : 1.0f, H, W, total);
+        vecint_step_kernel<<<cdiv(total, 256), 256, 0, s>>>(cur, dst, k == 0 ? scale : 1.0f, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
         CF_CHECK_LAUNCH("vecint_step_kernel");
         cur = dst;
     }

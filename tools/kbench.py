@@ -73,11 +73,13 @@ def want(k):
     return not args.only or k in args.only.split(",")
 
 
-if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24"):
+if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24", "cfg2h", "cfg2q"):
     P, C, H, W, IH = {"cfg2": (29, 256, 32, 32, 256), "cfg4": (64, 256, 64, 64, 512), "cfg1": (1, 256, 28, 28, 224),
-                      "ref24": (2, 256, 24, 24, 192)}[args.cfg]
+                      "ref24": (2, 256, 24, 24, 192), "cfg2h": (14, 256, 32, 32, 256), "cfg2q": (7, 256, 32, 32, 256)}[args.cfg]
     L, R = 4, 4
     nrot = 3 if args.cfg == "cfg2" else (2 if args.cfg == "cfg4" else 8)
+    if os.environ.get("KB_NROT"):
+        nrot = int(os.environ["KB_NROT"])
     torch.manual_seed(0)
     f1 = [torch.randn(P, C, H, W, device=dev) for _ in range(nrot)]
     f2 = [torch.randn(P, C, H, W, device=dev) for _ in range(nrot)]

@@ -53,12 +53,13 @@ int check_corr_shape(int B, int H, int W, int L, LevelDims* d) {
 
 using namespace cf;
 
-namespace cf { void corr_tcgen05_set_debug(float* p); }
+namespace cf { void corr_tcgen05_set_debug(float* p); void corr_tcgen05_set_timestamps(unsigned long long* p, int cta); }
 
 extern "C" {
 
 // bring-up hook, not part of the public header
 CF_API void cf_debug_set_gemm_dump(float* p) { cf::corr_tcgen05_set_debug(p); }
+CF_API void cf_debug_set_gemm_timestamps(unsigned long long* p, int cta) { cf::corr_tcgen05_set_timestamps(p, cta); }
 
 int cf_version(void) { return 100; }
 
@@ -100,19 +101,19 @@ int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, 
     int rc = check_corr_shape(B, H, W, L, &d);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    float* level0 = pyramid;
-    float* level1 = L > 1 ? reinterpret_cast<float*>(reinterpret_cast<char*>(pyramid) + d.off[1]) : nullptr;
+    float* levels[CF_MAX_LEVELS] = {};
+    for (int l = 0; l < L; ++l) levels[l] = reinterpret_cast<float*>(reinterpret_cast<char*>(pyramid) + d.off[l]);
 
     int from_level = 0;
     int used = CF_PREC_FP32;
     if (precision != CF_PREC_FP32) {
-        const bool fuse = level1 && corr_tcgen05_supported(B, C, H, W, true) && aligned16(f1) && aligned16(f2);
-        const bool plain = !fuse && corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2);
-        if (fuse || plain) {
-            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, level0, fuse ? level1 : nullptr, workspace, workspace_bytes, s);
+        // the GEMM fuses as many pooled levels into its epilogue as the shape allows (none .. all)
+        if (corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2)) {
+            int done = 1;
+            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, levels, L, workspace, workspace_bytes, &done, s);
             if (rc) return rc;
             used = CF_PREC_BF16;
-            from_level = fuse ? 1 : 0;
+            from_level = done - 1;
         } else if (precision == CF_PREC_BF16) {
             return fail(CF_ERR_UNSUPPORTED,
                         "cf_corr_build: shape B=%d C=%d H=%d W=%d does not fit the tcgen05 tiling "
@@ -121,7 +122,7 @@ int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, 
         }
     }
     if (used == CF_PREC_FP32) {
-        rc = launch_corr_simt(f1, f2, B, C, H * W, level0, s);
+        rc = launch_corr_simt(f1, f2, B, C, H * W, levels[0], s);
         if (rc) return rc;
     }
     if (used_precision) *used_precision = used;

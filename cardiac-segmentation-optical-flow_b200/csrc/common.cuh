@@ -100,8 +100,8 @@ int launch_pool_chain_bwd(float* gpyr, const LevelDims& d, long n_img, int L, cu
 
 int launch_corr_simt(const float* f1, const float* f2, int B, int C, int HW, float* level0, cudaStream_t s);
 // returns CF_ERR_UNSUPPORTED (without touching the stream) when the shape does not fit the TMA/UMMA tiling
-int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* level0,
-                        float* level1 /* may be null: no fused pooling */, void* workspace, size_t ws_bytes,
+int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* const* levels, int L,
+                        void* workspace, size_t ws_bytes, int* levels_done /* levels written by the GEMM */,
                         cudaStream_t s);
 size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W);
 bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool);

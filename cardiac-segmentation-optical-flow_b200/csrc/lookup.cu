@@ -294,6 +294,126 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     }
 }
 
+// Variant: ONE warp per CTA owns 32 queries x one level and evaluates all (2r+1)^2 outputs of its queries.  Nothing is
+// shared between warps and every per-query quantity (anchor, classification, x taps, staging setup) is computed exactly
+// once instead of once per warp of a 3-warp CTA; the output rows are processed in chunks of CH = 3 with a rolled loop
+// (register window (CH+1) x (2r+2), compact code).  Fewer instructions, fewer resident warps (one window buffer each).
+template <int R>
+__global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__ LookupParams P) {
+    using G = Geo<R>;
+    constexpr int SIDE = G::SIDE, PR = G::PR, PC = G::PC, K = SIDE * SIDE, CH = 3;
+    extern __shared__ __align__(16) float win[];     // windows: win_base(q) + row * PC + column
+
+    const int lane = threadIdx.x;
+    const unsigned task = P.lshift >= 0 ? (blockIdx.x >> P.lshift) : blockIdx.x / (unsigned)P.L;
+    const int l = (int)(blockIdx.x - task * (unsigned)P.L);
+    const unsigned n0 = task * kQT;             // CTA-uniform
+    const bool valid = n0 + lane < (unsigned)P.N;
+    const int hl = P.lh[l], wl = P.lw[l];
+    const bool vec = (wl & 3) == 0;
+    const unsigned HW = (unsigned)P.HW;
+
+    unsigned b = n0 / HW;
+    unsigned p = n0 - b * HW + lane;
+    if (p >= HW) { p -= HW; ++b; }                  // H*W >= 256 > 32: at most one wrap
+    float cx = 0.0f, cy = 0.0f;
+    if (valid) {
+        const float inv = __int_as_float((127 - l) << 23);      // 2^-l: the reference's division by 2^l, exactly
+        const float* cp = P.coords + (size_t)b * 2 * HW + p;
+        cx = __fmul_rn(__ldg(cp), inv);
+        cy = __fmul_rn(__ldg(cp + HW), inv);
+    }
+    const bool dead = !valid || !(fabsf(cx) < kDeadCoord) || !(fabsf(cy) < kDeadCoord);
+    if (dead) cx = cy = 0.0f;                       // finite taps; the outputs are forced to zero below
+    bool nom_x, nom_y, lo_x, lo_y;
+    classify<R>(cx, wl, nom_x, lo_x);
+    classify<R>(cy, hl, nom_y, lo_y);
+    const int ax = dead ? 0 : __float2int_rd(cx) - R - (lo_x ? 1 : 0);
+    const int ay = dead ? 0 : __float2int_rd(cy) - R - (lo_y ? 1 : 0);
+    const int sh = vec ? (ax & 3) : 0;
+    const bool fast = __all_sync(0xffffffffu, dead || (nom_x && nom_y));
+    {
+        const float* __restrict__ img0 = P.level[l] + (size_t)n0 * hl * wl;
+        const unsigned flags = (dead ? kDead : 0u) | (nom_x ? kNomX : 0u) | (nom_y ? kNomY : 0u) | (lo_x ? kLoX : 0u) |
+                               (lo_y ? kLoY : 0u);
+        const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
+        if (vec) stage_windows<R, 1, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
+        else stage_windows<R, 1, false>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
+    }
+    // x taps (registers) while the copies are in flight
+    float xl[SIDE], xh[SIDE];
+    int xo[SIDE];
+    {
+        const float s1x = (float)(wl - 1), rx = P.rcp_w[l];
+#pragma unroll
+        for (int i = 0; i < SIDE; ++i) {
+            int i0;
+            axis_tap(cx, i - R, s1x, rx, i0, xl[i], xh[i]);
+            xo[i] = min(max(i0 - ax, 0), PR - 2) + sh;
+        }
+    }
+    const float s1y = (float)(hl - 1), ry = P.rcp_h[l];
+    cp_async_wait_all();
+    __syncwarp();
+    if (!valid) return;
+
+    const float* sq = win + win_base<R>(lane);
+    // 32-bit element offsets from a per-lane base (L * K * HW < 2^30 is checked on the host)
+    float* const ob = P.out + ((size_t)b * P.L * K + (size_t)l * K) * HW + p;
+    const float* rp0 = sq + (lo_y ? PC : 0) + sh + (lo_x ? 1 : 0);
+#pragma unroll 1
+    for (int jc = 0; jc < SIDE; jc += CH) {
+        int yo[CH];
+        float yl[CH], yh[CH];
+#pragma unroll
+        for (int k = 0; k < CH; ++k) {
+            int j0 = 0;
+            yl[k] = yh[k] = 0.0f;
+            if (jc + k < SIDE) axis_tap(cy, jc + k - R, s1y, ry, j0, yl[k], yh[k]);
+            yo[k] = min(max(j0 - ay, 0), PR - 2) * PC;
+        }
+        if (fast) {
+            // nominal taps: with o = (lo ? 1 : 0), x tap i reads stored columns sh+o+i, +1; output row j reads rows o+j, +1
+            float r[CH + 1][SIDE + 1];
+            const float* rp = rp0 + jc * PC;
+#pragma unroll
+            for (int k = 0; k <= CH; ++k)
+#pragma unroll
+                for (int c = 0; c <= SIDE; ++c) r[k][c] = (!dead && jc + k <= SIDE) ? rp[k * PC + c] : 0.0f;
+#pragma unroll
+            for (int k = 0; k < CH; ++k) {
+                if (jc + k < SIDE) {
+                    unsigned off = (unsigned)(jc + k) * HW;
+#pragma unroll
+                    for (int i = 0; i < SIDE; ++i, off += SIDE * HW) {
+                        float acc = __fmul_rn(r[k][i], __fmul_rn(xl[i], yl[k]));
+                        acc = fmaf(r[k][i + 1], __fmul_rn(xh[i], yl[k]), acc);
+                        acc = fmaf(r[k + 1][i], __fmul_rn(xl[i], yh[k]), acc);
+                        acc = fmaf(r[k + 1][i + 1], __fmul_rn(xh[i], yh[k]), acc);
+                        __stcs(ob + off, acc);
+                    }
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < CH; ++k) {
+                if (jc + k < SIDE) {
+                    unsigned off = (unsigned)(jc + k) * HW;
+#pragma unroll
+                    for (int i = 0; i < SIDE; ++i, off += SIDE * HW) {
+                        const float* t = sq + yo[k] + xo[i];
+                        float acc = __fmul_rn(t[0], __fmul_rn(xl[i], yl[k]));
+                        acc = fmaf(t[1], __fmul_rn(xh[i], yl[k]), acc);
+                        acc = fmaf(t[PC], __fmul_rn(xl[i], yh[k]), acc);
+                        acc = fmaf(t[PC + 1], __fmul_rn(xh[i], yh[k]), acc);
+                        __stcs(ob + off, dead ? 0.0f : acc);
+                    }
+                }
+            }
+        }
+    }
+}
+
 template <int R>
 __global__ void __launch_bounds__(128) lookup_taps_kernel(const __grid_constant__ LookupParams P) {
     using G = Geo<R>;
@@ -333,6 +453,12 @@ int launch_lookup_r(const LookupParams& P, cudaStream_t s) {
     const long ngroups = (P.N + kQT - 1) / kQT;
     if (P.N > 0x7fffffffL || ngroups * P.L > 0x7fffffffL) return fail(CF_ERR_UNSUPPORTED, "lookup grid too large (%ld queries)", P.N);
     static const int nw = [] { const char* e = getenv("CF_LOOKUP_NW"); return e ? atoi(e) : 3; }();   // tuning knob
+    if ((long)P.L * Geo<R>::SIDE * Geo<R>::SIDE * P.HW < (1L << 30) && nw == 1) {
+        constexpr size_t smem = (size_t)Geo<R>::WIN * sizeof(float);
+        lookup_warp_kernel<R><<<(unsigned)(ngroups * P.L), 32, smem, s>>>(P);
+        CF_CHECK_LAUNCH("lookup_warp_kernel");
+        return CF_OK;
+    }
     switch (nw) {
         case 2: return launch_lookup_rw<R, 2>(P, ngroups, s);
         case 4: return launch_lookup_rw<R, 4>(P, ngroups, s);

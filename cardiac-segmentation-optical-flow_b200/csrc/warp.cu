@@ -4,63 +4,98 @@
 // add + 2 normalise kernels + permute + channel-swap gather + grid_sampler_2d (6 launches, ~4x the
 // compulsory traffic on the coordinate tensor).  Here: one launch, flow read once (128-bit), all C channels
 // sampled per pixel from the taps computed once, 128-bit stores.  HBM-bound: 4*H*W*(2C+2) bytes per item.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "sampling.cuh"
 
 namespace cf {
 namespace {
 
+// One thread = VEC horizontally adjacent pixels of one image, all C channels.  Everything that does not depend on the
+// channel (coordinates, weights, tap offsets, in-image masks) is computed once per pixel; the channel loop is 4
+// predicated loads + 1 multiply + 3 FMAs per pixel, 32-bit index arithmetic throughout.
 template <int VEC, int MODE>
-__global__ void __launch_bounds__(256) warp2d_kernel(const float* __restrict__ flow, const float* __restrict__ src,
-                                                     float* __restrict__ out, int C, int H, int W, float ry, float rx,
-                                                     long total) {
-    const long t = (long)blockIdx.x * 256 + threadIdx.x;
-    if (t >= total) return;
-    const int wv = W / VEC;
-    const int x = (int)(t % wv) * VEC;
-    const long row = t / wv;
-    const int y = (int)(row % H);
-    const long b = row / H;
-    const size_t HW = (size_t)H * W, pix = (size_t)y * W + x;
+__global__ void __launch_bounds__(256, VEC == 2 ? 5 : (VEC == 4 ? 3 : 1)) warp2d_kernel(const float* __restrict__ flow, const float* __restrict__ src,
+                                                     float* __restrict__ out, int B, int C, int H, int W, float ry, float rx,
+                                                     int wv_shift) {
+    const unsigned wv = (unsigned)W / VEC;
+    const unsigned t = blockIdx.x * 256u + threadIdx.x;          // position inside one image
+    if (t >= (unsigned)H * wv) return;
+    const unsigned y = wv_shift >= 0 ? (t >> wv_shift) : t / wv;
+    const unsigned x = (t - y * wv) * VEC;
+    const unsigned HW = (unsigned)(H * W), pix = y * (unsigned)W + x;
     const float s1y = (float)(H - 1), s1x = (float)(W - 1);
 
-    float dy[VEC], dx[VEC];
-    const float* fyp = flow + (b * 2 + 0) * HW + pix;
-    const float* fxp = flow + (b * 2 + 1) * HW + pix;
-    if (VEC == 4) {
-        const float4 a = ldg_f4(fyp), c = ldg_f4(fxp);
-        dy[0] = a.x; dy[1 % VEC] = a.y; dy[2 % VEC] = a.z; dy[3 % VEC] = a.w;
-        dx[0] = c.x; dx[1 % VEC] = c.y; dx[2 % VEC] = c.z; dx[3 % VEC] = c.w;
-    } else {
-        dy[0] = __ldg(fyp);
-        dx[0] = __ldg(fxp);
-    }
-
-    Tap tap[VEC];
-    int ny[VEC], nx[VEC];
-#pragma unroll
-    for (int v = 0; v < VEC; ++v) {
-        const float uy = warp_coord(__fadd_rn((float)y, dy[v]), s1y, ry);
-        const float ux = warp_coord(__fadd_rn((float)(x + v), dx[v]), s1x, rx);
-        if (MODE == CF_MODE_BILINEAR) {
-            tap[v] = make_tap(uy, ux);
-        } else {  // ATen nearest: nearbyint = round half to even
-            ny[v] = __float2int_rn(uy);
-            nx[v] = __float2int_rn(ux);
-        }
-    }
-
-    for (int c = 0; c < C; ++c) {
-        const float* img = src + (b * C + c) * HW;
-        float r[VEC];
-#pragma unroll
-        for (int v = 0; v < VEC; ++v)
-            r[v] = (MODE == CF_MODE_BILINEAR) ? sample_bilinear(img, H, W, tap[v]) : fetch(img, H, W, ny[v], nx[v]);
-        float* o = out + (b * C + c) * HW + pix;
+    for (unsigned b = blockIdx.y; b < (unsigned)B; b += gridDim.y) {
+        float dy[VEC], dx[VEC];
+        const float* fyp = flow + ((size_t)b * 2 + 0) * HW + pix;
+        const float* fxp = fyp + HW;
         if (VEC == 4) {
-            *reinterpret_cast<float4*>(o) = make_float4(r[0], r[1 % VEC], r[2 % VEC], r[3 % VEC]);
+            const float4 a = ldg_f4(fyp), c = ldg_f4(fxp);
+            dy[0] = a.x; dy[1 % VEC] = a.y; dy[2 % VEC] = a.z; dy[3 % VEC] = a.w;
+            dx[0] = c.x; dx[1 % VEC] = c.y; dx[2 % VEC] = c.z; dx[3 % VEC] = c.w;
+        } else if (VEC == 2) {
+            const float2 a = __ldg(reinterpret_cast<const float2*>(fyp)), c = __ldg(reinterpret_cast<const float2*>(fxp));
+            dy[0] = a.x; dy[1 % VEC] = a.y;
+            dx[0] = c.x; dx[1 % VEC] = c.y;
         } else {
-            o[0] = r[0];
+            dy[0] = __ldg(fyp);
+            dx[0] = __ldg(fxp);
+        }
+
+        // Tap offsets are clamped into the image and loaded unconditionally (straight-line code, every load of a pixel in
+        // flight at once); a tap outside the image is replaced by zero afterwards (zero padding), never multiplied in.
+        int off[VEC][4];       // nw, ne, sw, se (bilinear) / [0] = nearest texel
+        unsigned msk[VEC];     // bit k: tap k lies inside the image
+        float w00[VEC], w01[VEC], w10[VEC], w11[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            const float uy = warp_coord(__fadd_rn((float)y, dy[v]), s1y, ry);
+            const float ux = warp_coord(__fadd_rn((float)(x + v), dx[v]), s1x, rx);
+            if (MODE == CF_MODE_BILINEAR) {
+                const Tap tp = make_tap(uy, ux);
+                const bool y0 = (unsigned)tp.y0 < (unsigned)H, y1 = (unsigned)(tp.y0 + 1) < (unsigned)H;
+                const bool x0 = (unsigned)tp.x0 < (unsigned)W, x1 = (unsigned)(tp.x0 + 1) < (unsigned)W;
+                msk[v] = (y0 && x0 ? 1u : 0u) | (y0 && x1 ? 2u : 0u) | (y1 && x0 ? 4u : 0u) | (y1 && x1 ? 8u : 0u);
+                const int r0 = (y0 ? tp.y0 : 0) * W, r1 = (y1 ? tp.y0 + 1 : 0) * W;
+                const int c0 = x0 ? tp.x0 : 0, c1 = x1 ? tp.x0 + 1 : 0;
+                off[v][0] = r0 + c0; off[v][1] = r0 + c1; off[v][2] = r1 + c0; off[v][3] = r1 + c1;
+                w00[v] = tp.w00; w01[v] = tp.w01; w10[v] = tp.w10; w11[v] = tp.w11;
+            } else {  // ATen nearest: nearbyint = round half to even
+                const int ny = __float2int_rn(uy), nx = __float2int_rn(ux);
+                const bool in = (unsigned)ny < (unsigned)H && (unsigned)nx < (unsigned)W;
+                msk[v] = in ? 1u : 0u;
+                off[v][0] = in ? ny * W + nx : 0;
+                off[v][1] = off[v][2] = off[v][3] = 0;
+                w00[v] = w01[v] = w10[v] = w11[v] = 0.0f;
+            }
+        }
+
+        const float* img = src + (size_t)b * C * HW;
+        float* o = out + (size_t)b * C * HW + pix;
+        for (int c = 0; c < C; ++c, img += HW, o += HW) {
+            float r[VEC];
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) {
+                if (MODE == CF_MODE_BILINEAR) {
+                    const float l00 = __ldg(img + off[v][0]), l01 = __ldg(img + off[v][1]);
+                    const float l10 = __ldg(img + off[v][2]), l11 = __ldg(img + off[v][3]);
+                    const float v00 = (msk[v] & 1u) ? l00 : 0.0f, v01 = (msk[v] & 2u) ? l01 : 0.0f;
+                    const float v10 = (msk[v] & 4u) ? l10 : 0.0f, v11 = (msk[v] & 8u) ? l11 : 0.0f;
+                    float acc = __fmul_rn(v00, w00[v]);      // ATen order: nw, ne, sw, se
+                    acc = fmaf(v01, w01[v], acc);
+                    acc = fmaf(v10, w10[v], acc);
+                    acc = fmaf(v11, w11[v], acc);
+                    r[v] = acc;
+                } else {
+                    const float l00 = __ldg(img + off[v][0]);
+                    r[v] = (msk[v] & 1u) ? l00 : 0.0f;
+                }
+            }
+            if (VEC == 4) *reinterpret_cast<float4*>(o) = make_float4(r[0], r[1 % VEC], r[2 % VEC], r[3 % VEC]);
+            else if (VEC == 2) *reinterpret_cast<float2*>(o) = make_float2(r[0], r[1 % VEC]);
+            else o[0] = r[0];
         }
     }
 }
@@ -140,16 +175,24 @@ int launch_coords_grid(float* out, int B, int H, int W, cudaStream_t s) {
 
 int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int W, int mode, float* out,
                   cudaStream_t s) {
+    if ((long)H * W >= (1L << 30)) return fail(CF_ERR_UNSUPPORTED, "warp2d: image of %dx%d pixels too large", H, W);
+    static const int want = [] { const char* e = getenv("CF_WARP_VEC"); return e ? atoi(e) : 2; }();   // tuning knob (measured: 2 > 4 > 1)
     const bool vec = (W % 4 == 0) && aligned16(flow) && aligned16(src) && aligned16(out);
-    const long total = (long)B * H * (vec ? W / 4 : W);
-    const int grid = cdiv(total, 256);
+    const int nv = vec ? (want == 4 ? 4 : 2) : 1;
+    const unsigned wv = (unsigned)(W / nv);
+    int wv_shift = -1;
+    for (int k = 0; k < 31; ++k)
+        if ((1u << k) == wv) wv_shift = k;
+    const dim3 grid((unsigned)cdiv((long)H * wv, 256), (unsigned)(B < 65535 ? B : 65535));
     const float ry = 1.0f / (float)(H - 1), rx = 1.0f / (float)(W - 1);   // IEEE-rounded reciprocals for div_small
     if (mode == CF_MODE_BILINEAR) {
-        if (vec) warp2d_kernel<4, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
-        else warp2d_kernel<1, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
+        if (nv == 4) warp2d_kernel<4, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry, rx, wv_shift);
+        else if (nv == 2) warp2d_kernel<2, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry, rx, wv_shift);
+        else warp2d_kernel<1, CF_MODE_BILINEAR><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry, rx, wv_shift);
     } else {
-        if (vec) warp2d_kernel<4, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
-        else warp2d_kernel<1, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, C, H, W, ry, rx, total);
+        if (nv == 4) warp2d_kernel<4, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry, rx, wv_shift);
+        else if (nv == 2) warp2d_kernel<2, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry, rx, wv_shift);
+        else warp2d_kernel<1, CF_MODE_NEAREST><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry, rx, wv_shift);
     }
     CF_CHECK_LAUNCH("warp2d_kernel");
     return CF_OK;

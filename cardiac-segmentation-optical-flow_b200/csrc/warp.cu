@@ -100,6 +100,103 @@ __global__ void __launch_bounds__(256, VEC == 2 ? 5 : (VEC == 4 ? 3 : 1)) warp2d
     }
 }
 
+// ---- bilinear, tiled (the production path) ----
+// A warp covers 32 consecutive pixels of 2 image rows (lane = column, a thread samples (x, y) and (x, y + 1)), a CTA
+// 32 x 16 pixels.  The bound is the L1 wavefront rate of the gathers (ncu: l1tex data-pipe 75-80 % with a 16 x 4 warp
+// tile, 20 sectors per request), so lanes run along a row: a tap load of a warp touches 1-2 lines.  The kernel votes
+// once per warp: when every tap of every lane is inside the image and every coordinate is in div_small's checked range,
+// the channel loop is 4 unpredicated loads at o, o+1, o+W, o+W+1 + 1 FMUL + 3 FFMA per pixel with ONE offset per
+// pixel; any other warp (image border, flow pointing outside) takes the general path (bounds-checked taps, IEEE
+// division).
+// The coordinate round trip is shortened without changing a bit: with t = RN(p/s1 - 0.5), the reference's
+// ((2t + 1) * 0.5) * s1 has exact doublings / halvings, so u = RN(RN(2t + 1) * (s1/2)) = fmul(fma(t, 2, 1), s1/2).
+__device__ __forceinline__ float warp_coord_lean(float p, float s1, float r, float hs1) {
+    const float t = __fsub_rn(div_small(p, s1, r), 0.5f);
+    return __fmul_rn(__fmaf_rn(t, 2.0f, 1.0f), hs1);
+}
+
+// general path of the tiled kernel (rare: border warps), kept out of line so that it does not set the register budget
+__device__ __noinline__ void warp2d_general(const float* __restrict__ img, float* __restrict__ o, int C, int H, int W,
+                                            float py, float px, float ry, float rx) {
+    const unsigned HW = (unsigned)(H * W);
+    const Tap t = make_tap(warp_coord(py, (float)(H - 1), ry), warp_coord(px, (float)(W - 1), rx));
+#pragma unroll 1
+    for (int c = 0; c < C; ++c, img += HW, o += HW) *o = sample_bilinear(img, H, W, t);
+}
+
+constexpr int kTileW = 32, kTileH = 16;   // CTA tile: 8 warps, each 32 pixels x 2 rows (lane = column)
+
+template <bool FASTDIV>
+__global__ void __launch_bounds__(256, 4) warp2d_tile_kernel(const float* __restrict__ flow, const float* __restrict__ src,
+                                                             float* __restrict__ out, int B, int C, int H, int W, float ry,
+                                                             float rx) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int x = blockIdx.x * kTileW + lane;
+    const int y = blockIdx.y * kTileH + wid * 2;
+    const bool act0 = x < W && y < H, act1 = x < W && y + 1 < H;
+    const unsigned HW = (unsigned)(H * W), pix = (unsigned)y * (unsigned)W + (unsigned)x;
+    const float s1y = (float)(H - 1), s1x = (float)(W - 1), hs1y = 0.5f * s1y, hs1x = 0.5f * s1x;
+    const float yf0 = (float)y, yf1 = (float)(y + 1), xf = (float)x;
+
+    // The chain flow load -> coordinates -> gathers -> store is two DRAM latencies long and a thread keeps only 16 B of
+    // flow in flight: the flow of the NEXT image of this thread is loaded before the current one is sampled.
+    float nfy0 = 0.f, nfy1 = 0.f, nfx0 = 0.f, nfx1 = 0.f;
+    if (blockIdx.z < (unsigned)B) {
+        const float* fyp = flow + ((size_t)blockIdx.z * 2) * HW + pix;
+        if (act0) { nfy0 = __ldcs(fyp); nfx0 = __ldcs(fyp + HW); }
+        if (act1) { nfy1 = __ldcs(fyp + W); nfx1 = __ldcs(fyp + HW + W); }
+    }
+    for (unsigned b = blockIdx.z; b < (unsigned)B; b += gridDim.z) {
+        const float fy0 = nfy0, fy1 = nfy1, fx0 = nfx0, fx1 = nfx1;
+        if (b + gridDim.z < (unsigned)B) {
+            const float* fyp = flow + ((size_t)(b + gridDim.z) * 2) * HW + pix;
+            if (act0) { nfy0 = __ldcs(fyp); nfx0 = __ldcs(fyp + HW); }
+            if (act1) { nfy1 = __ldcs(fyp + W); nfx1 = __ldcs(fyp + HW + W); }
+        }
+        const float py0 = __fadd_rn(yf0, fy0), py1 = __fadd_rn(yf1, fy1);
+        const float px0 = __fadd_rn(xf, fx0), px1 = __fadd_rn(xf, fx1);
+        bool ok = FASTDIV && fabsf(py0) < 16384.0f && fabsf(py1) < 16384.0f && fabsf(px0) < 16384.0f && fabsf(px1) < 16384.0f;
+        const float uy0 = warp_coord_lean(py0, s1y, ry, hs1y), uy1 = warp_coord_lean(py1, s1y, ry, hs1y);
+        const float ux0 = warp_coord_lean(px0, s1x, rx, hs1x), ux1 = warp_coord_lean(px1, s1x, rx, hs1x);
+        const float gy0 = floorf(uy0), gy1 = floorf(uy1), gx0 = floorf(ux0), gx1 = floorf(ux1);
+        const int iy0 = (int)gy0, iy1 = (int)gy1, ix0 = (int)gx0, ix1 = (int)gx1;
+        ok = ok && (unsigned)iy0 < (unsigned)(H - 1) && (unsigned)iy1 < (unsigned)(H - 1) &&
+             (unsigned)ix0 < (unsigned)(W - 1) && (unsigned)ix1 < (unsigned)(W - 1);
+        const float* img = src + (size_t)b * C * HW;
+        float* o = out + (size_t)b * C * HW + pix;
+        if (__all_sync(0xffffffffu, ok && act1)) {
+            // weights in make_tap's order of operations
+            const float ah0 = __fsub_rn(ux0, gx0), al0 = __fsub_rn(__fadd_rn(gx0, 1.0f), ux0);
+            const float bh0 = __fsub_rn(uy0, gy0), bl0 = __fsub_rn(__fadd_rn(gy0, 1.0f), uy0);
+            const float ah1 = __fsub_rn(ux1, gx1), al1 = __fsub_rn(__fadd_rn(gx1, 1.0f), ux1);
+            const float bh1 = __fsub_rn(uy1, gy1), bl1 = __fsub_rn(__fadd_rn(gy1, 1.0f), uy1);
+            const float w00a = __fmul_rn(al0, bl0), w01a = __fmul_rn(ah0, bl0), w10a = __fmul_rn(al0, bh0), w11a = __fmul_rn(ah0, bh0);
+            const float w00b = __fmul_rn(al1, bl1), w01b = __fmul_rn(ah1, bl1), w10b = __fmul_rn(al1, bh1), w11b = __fmul_rn(ah1, bh1);
+            const float* pa = img + (iy0 * W + ix0);
+            const float* pb = img + (iy1 * W + ix1);
+#pragma unroll 2
+            for (int c = 0; c < C; ++c, pa += HW, pb += HW, o += HW) {
+                const float a00 = __ldg(pa), a01 = __ldg(pa + 1), a10 = __ldg(pa + W), a11 = __ldg(pa + W + 1);
+                const float b00 = __ldg(pb), b01 = __ldg(pb + 1), b10 = __ldg(pb + W), b11 = __ldg(pb + W + 1);
+                float ra = __fmul_rn(a00, w00a);          // ATen order: nw, ne, sw, se
+                ra = fmaf(a01, w01a, ra);
+                ra = fmaf(a10, w10a, ra);
+                ra = fmaf(a11, w11a, ra);
+                float rb = __fmul_rn(b00, w00b);
+                rb = fmaf(b01, w01b, rb);
+                rb = fmaf(b10, w10b, rb);
+                rb = fmaf(b11, w11b, rb);
+                __stcs(o, ra);
+                __stcs(o + W, rb);
+            }
+        } else {
+            // general path: the reference's sequence with the range-checked division and per-tap bounds checks
+            if (act0) warp2d_general(img, o, C, H, W, py0, px0, ry, rx);
+            if (act1) warp2d_general(img, o + W, C, H, W, py1, px1, ry, rx);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) warp2d_taps_kernel(const float* __restrict__ flow, float* __restrict__ taps,
                                                           int H, int W, float ry, float rx, long total) {
     const long t = (long)blockIdx.x * 256 + threadIdx.x;
@@ -176,7 +273,21 @@ int launch_coords_grid(float* out, int B, int H, int W, cudaStream_t s) {
 int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int W, int mode, float* out,
                   cudaStream_t s) {
     if ((long)H * W >= (1L << 30)) return fail(CF_ERR_UNSUPPORTED, "warp2d: image of %dx%d pixels too large", H, W);
-    static const int want = [] { const char* e = getenv("CF_WARP_VEC"); return e ? atoi(e) : 2; }();   // tuning knob (measured: 2 > 4 > 1)
+    static const int want = [] { const char* e = getenv("CF_WARP_VEC"); return e ? atoi(e) : 0; }();   // tuning knob: 0 = tiled kernel
+    const float ry_ = 1.0f / (float)(H - 1), rx_ = 1.0f / (float)(W - 1);   // IEEE-rounded reciprocals for div_small
+    if (want == 0 && mode == CF_MODE_BILINEAR) {
+        const int tiles_x = cdiv(W, kTileW), tiles_y = cdiv(H, kTileH);
+        // a thread's setup (tile position, constants) is amortised over a few images once the grid fills the machine
+        static const int target = [] { const char* e = getenv("CF_WARP_CTAS"); return e ? atoi(e) : 2368; }();   // 148 SMs x 4 resident CTAs x 4 (measured: 1184 < 2368 ~ 4736)
+        long gz = (target + (long)tiles_x * tiles_y - 1) / ((long)tiles_x * tiles_y);
+        gz = gz < 1 ? 1 : (gz > B ? B : (gz > 65535 ? 65535 : gz));
+        const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)gz);
+        if (tiles_y > 65535) return fail(CF_ERR_UNSUPPORTED, "warp2d: image height %d too large", H);
+        if (H - 1 <= 4095 && W - 1 <= 4095) warp2d_tile_kernel<true><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_);
+        else warp2d_tile_kernel<false><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_);
+        CF_CHECK_LAUNCH("warp2d_tile_kernel");
+        return CF_OK;
+    }
     const bool vec = (W % 4 == 0) && aligned16(flow) && aligned16(src) && aligned16(out);
     const int nv = vec ? (want == 4 ? 4 : 2) : 1;
     const unsigned wv = (unsigned)(W / nv);

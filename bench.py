@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the optical-flow hot path: frame-pairs/sec for (correlation pyramid build + 12 lookups + warp).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg4] [--no-graph]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg4|cfg5 [--patients P --slices S]] [--no-graph]
 
 One "step" = one (patient, slice) cine unit of BASELINE.json configs[1]: 29 consecutive frame pairs with
 256-channel 32x32 feature maps -> CorrBlock build (batched over the 29 pairs), 12 CorrBlock lookups, and the
@@ -32,6 +32,9 @@ WORKLOADS = {
     # name: pairs, C, fmap H, W, image H, W
     "cfg2": dict(pairs=29, C=256, H=32, W=32, IH=256, IW=256,
                  desc="configs[1]: 29 frame pairs, 256-ch fmaps 32x32 (256^2 input), 4 levels, r=4, 12 lookups, 29 warps"),
+    "cfg5": dict(pairs=29, C=256, H=32, W=32, IH=256, IW=256,
+                 desc="configs[4]: cohort of patients x slices cine units (29 pairs each, 32x32 fmaps, 256^2 frames + 4-class masks), "
+                      "sharded by (patient, slice), one NCCL gather"),
     "cfg4": dict(pairs=64, C=256, H=64, W=64, IH=512, IW=512,
                  desc="configs[3]: 64 frame pairs, 256-ch fmaps 64x64, materialised volume, 12 lookups, 64 warps"),
 }
@@ -152,7 +155,7 @@ def run_reference_arm(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = 4 if args.workload == "cfg2" else 1
+    sample = 1 if args.workload == "cfg4" else 4
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     from oracle import corr_oracle, warp_oracle
@@ -187,6 +190,149 @@ def run_reference_arm(args, wl):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------ cfg5 cohort
+def make_unit_device(wl, seed, dev):
+    """cfg5 unit generated ON the device from its own seed (any rank can build any unit): the cfg2 recipe plus a
+    4-class label map (concentric-ring phantom) that is warped through one-hot/argmax."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    P, C, H, W, IH, IW = wl["pairs"], wl["C"], wl["H"], wl["W"], wl["IH"], wl["IW"]
+    frames = torch.randn(P + 1, C, H, W, generator=g, device=dev)
+    frames[1:] = 0.9 * frames[:-1].roll(shifts=(1, 1), dims=(2, 3)) + 0.45 * frames[1:]
+    ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
+    grid = torch.stack([xs, ys]).float()[None]
+    steps = torch.randn(ITERS, P, 2, H, W, generator=g, device=dev) * 0.5
+    steps[0] = 0
+    coords = grid + steps.cumsum(0)
+    coords[:, :, 0].clamp_(-4, W + 4)
+    coords[:, :, 1].clamp_(-4, H + 4)
+    img = torch.rand(P, 1, IH, IW, generator=g, device=dev)
+    flow = torch.nn.functional.interpolate(torch.randn(P, 2, 9, 9, generator=g, device=dev) * 3.0, size=(IH, IW),
+                                           mode="bicubic", align_corners=True).contiguous()
+    yy, xx = torch.meshgrid(torch.arange(IH, device=dev), torch.arange(IW, device=dev), indexing="ij")
+    rad = ((yy - IH / 2) ** 2 + (xx - IW / 2) ** 2).float().sqrt() / (IH / 2)
+    label = (rad < 0.2).long() * 3 + ((rad >= 0.2) & (rad < 0.35)).long() * 2 + ((rad >= 0.35) & (rad < 0.6)).long()
+    label = label[None, None].repeat(P, 1, 1, 1).contiguous()
+    return dict(f1=frames[:-1].contiguous(), f2=frames[1:].contiguous(), coords=coords.contiguous(), img=img, flow=flow,
+                label=label)
+
+
+def run_cohort(args, wl):
+    """BASELINE.json configs[4]: the whole synthetic cohort sharded by (patient, slice) over the ranks, no data-path
+    collective, ONE NCCL all_gather of the compact per-unit result rows at the end (cardioflow_b200.shard)."""
+    import cardioflow_b200 as cf
+    from cardioflow_b200 import _cabi, shard
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        sys.exit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _cabi.lib()
+    P, H, W, IH, IW = wl["pairs"], wl["H"], wl["W"], wl["IH"], wl["IW"]
+    K81 = LEVELS * (2 * RADIUS + 1) ** 2
+    units = shard.cohort_units(args.patients, args.slices)
+    mine = shard.shard_units(units, rank, world)
+    pyramid = torch.empty(lib.cf_corr_pyramid_bytes(P, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
+    outs = torch.empty(ITERS, P, K81, H, W, dtype=torch.float32, device=dev)
+    warped = torch.empty(P, 1, IH, IW, dtype=torch.float32, device=dev)
+    WIDTH = 6   # row: [checksum of the last lookup, sum of the warped frames, 4 warped-label pixel counts]
+
+    def compute(u, row):
+        blk = cf.CorrBlock(u["f1"], u["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision, pyramid_buffer=pyramid)
+        for k in range(ITERS):
+            blk(u["coords"][k], out=outs[k])
+        cf.warp(u["img"], u["flow"], out=warped)
+        lab = cf.warp_onehot_argmax(u["flow"], u["label"], num_classes=4)
+        row[0] = outs[ITERS - 1].sum(dtype=torch.float64)
+        row[1] = warped.sum(dtype=torch.float64)
+        for c in range(4):
+            row[2 + c] = (lab == c).sum()
+
+    with torch.no_grad():
+        rows = torch.zeros(max(len(mine), 1), WIDTH, dtype=torch.float64, device=dev)
+        # static input buffers + ONE CUDA graph of a unit's whole device work (replayed per unit)
+        static = make_unit_device(wl, shard.unit_seed(*units[0]), dev)
+        row_buf = torch.zeros(WIDTH, dtype=torch.float64, device=dev)
+        compute(static, row_buf)
+        torch.cuda.synchronize()
+        graph = None
+        if not args.no_graph:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                compute(static, row_buf)
+
+        def run_unit(seed, dst):
+            u = make_unit_device(wl, seed, dev)              # input synthesis: not part of the path, not timed
+            for k, v in u.items():
+                static[k].copy_(v)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if graph:
+                graph.replay()
+            else:
+                compute(static, row_buf)
+            dst.copy_(row_buf)
+            e1.record()
+            return e0, e1
+
+        scratch = torch.zeros(WIDTH, dtype=torch.float64, device=dev)
+        for _ in range(max(args.warmup, 3)):
+            run_unit(shard.unit_seed(*units[0]), scratch)
+        if dist:                                             # communicator set-up is not part of the gather being timed
+            shard.gather_results(rows[:len(mine)], len(units), rank=rank, world_size=world)
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        evs = [run_unit(shard.unit_seed(pat, sl), rows[i]) for i, (pat, sl) in enumerate(mine)]
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        table = shard.gather_results(rows[:len(mine)], len(units), rank=rank, world_size=world)
+        g1.record()
+        torch.cuda.synchronize()
+        clocks = sampler.stop()
+        compute_ms = sum(a.elapsed_time(b) for a, b in evs)
+        gather_ms = g0.elapsed_time(g1)
+        # the gathered table must equal what any rank computes for a unit on its own (deterministic kernels)
+        check = []
+        if rank == 0:
+            for j in sorted({0, len(units) // 2, len(units) - 1, min(1, len(units) - 1)}):
+                run_unit(shard.unit_seed(*units[j]), scratch)
+                check.append(bool(torch.equal(scratch, table[j])))
+            torch.cuda.synchronize()
+    t = torch.tensor([compute_ms + gather_ms, compute_ms, gather_ms], dtype=torch.float64, device=dev)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, compute_ms, gather_ms = t.tolist()
+    if rank == 0:
+        n_pairs = len(units) * P
+        line = {
+            "metric": METRIC, "value": n_pairs / (total_ms * 1e-3), "unit": "frame-pairs/s", "n_gpus": world,
+            "steps": len(units), "warmup": max(args.warmup, 3), "ms_per_step": total_ms / max(len(mine), 1),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16 GEMM (fp32 accumulate) / f32 lookup+warp", "data": "synthetic",
+            "config": {"workload": "cfg5: " + wl["desc"], "patients": args.patients, "slices": args.slices,
+                       "units": len(units), "units_on_rank0": len(mine), "pairs_per_unit": P,
+                       "launch": "eager launches from Python, one unit at a time" if args.no_graph else "one CUDA graph replay per unit (build + 12 lookups + warp + mask warp + result row)",
+                       "l2": "every unit has fresh inputs and writes 623 MB (> 126 MB L2)"},
+            "clocks": clocks, "compute_ms_max_rank": compute_ms, "gather_ms_max_rank": gather_ms,
+            "gather": {"collective": "all_gather_into_tensor (NCCL)" if world > 1 else "none (1 rank)",
+                       "bytes_per_rank": int(rows[:len(mine)].numel() * 8), "rows_verified_on_rank0": check},
+            "gpu_launches": len(mine) * (2 + ITERS + 2),
+        }
+        if not all(check):
+            line["error"] = "gathered rows differ from a local recomputation"
+        print(json.dumps(line), flush=True)
+    if dist:
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------------------ GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -199,12 +345,16 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying one CUDA graph per step")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--patients", type=int, default=150, help="cfg5 only")
+    ap.add_argument("--slices", type=int, default=10, help="cfg5 only")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":
         return run_reference_arm(args, wl)
+    if args.workload == "cfg5":
+        return run_cohort(args, wl)
 
     import cardioflow_b200 as cf
     from cardioflow_b200 import _cabi
@@ -412,7 +562,7 @@ def main():
                      "frac_of_nominal_8000": achieved / 8000.0},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sample = 4 if args.workload == "cfg2" else 1
+        sample = 1 if args.workload == "cfg4" else 4
         v, cores, reps = cpu_pairs_per_sec(wl, sample)
         line["cpu_baseline"] = {"value": v, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
                                 "sample": f"{sample} of {P} pairs (per-pair CorrBlock + 12 lookups + warp), "

@@ -166,6 +166,10 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     float* const win = smem;                    // windows: win_base(q) + row * PC + column
     float* const xt = smem + G::WIN;            // [SIDE][3][kQT]: x taps (window column, w_lo, w_hi)
 
+    // Programmatic dependent launch: let the NEXT kernel of the stream (normally the next lookup) be scheduled while this
+    // grid drains -- its CTAs become resident and run their index arithmetic, then block in griddepcontrol.wait below
+    // until this grid has completed and flushed.  No effect on launches made without the PDL attribute.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     // levels interleave in launch order (read-heavy fine levels next to store-heavy coarse ones)
     const unsigned task = P.lshift >= 0 ? (blockIdx.x >> P.lshift) : blockIdx.x / (unsigned)P.L;
@@ -180,6 +184,8 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     unsigned p = n0 - b * (unsigned)P.HW + lane;
     if (p >= (unsigned)P.HW) { p -= (unsigned)P.HW; ++b; }      // H*W >= 256 > 32: at most one wrap
     float cx = 0.0f, cy = 0.0f;
+    // everything below reads memory the preceding kernels wrote (coords, pyramid) and writes `out`
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (valid) {
         const float inv = __int_as_float((127 - l) << 23);      // 2^-l: the reference's division by 2^l, exactly
         const float* cp = P.coords + (size_t)b * 2 * P.HW + p;
@@ -443,8 +449,18 @@ __global__ void __launch_bounds__(128) lookup_taps_kernel(const __grid_constant_
 
 template <int R, int NW>
 int launch_lookup_rw(const LookupParams& P, long ngroups, cudaStream_t s) {
-    lookup_kernel<R, NW><<<(unsigned)(ngroups * P.L), 32 * NW, Geo<R>::SMEM, s>>>(P);
-    CF_CHECK_LAUNCH("lookup_kernel");
+    static const bool pdl = [] { const char* e = getenv("CF_PDL"); return e ? atoi(e) != 0 : true; }();   // tuning knob
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(ngroups * P.L));
+    cfg.blockDim = dim3(32 * NW);
+    cfg.dynamicSmemBytes = Geo<R>::SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    CF_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lookup_kernel<R, NW>, P));
     return CF_OK;
 }
 

@@ -6,7 +6,8 @@ dispatch, no CPU fallback.  Import name: ``cardioflow_b200`` (alias package at t
 name carries a hyphen and cannot be imported directly).
 """
 from .corr import CorrBlock, coords_grid, lookup_taps
+from .upsample import upsample_flow, upsample_seg
 from .warp import SpatialTransformer, SpatialTransformerContour, VecInt, warp, warp_onehot_argmax, warp_taps
 
 __all__ = ["CorrBlock", "coords_grid", "lookup_taps", "SpatialTransformer", "SpatialTransformerContour", "VecInt",
-           "warp", "warp_onehot_argmax", "warp_taps"]
+           "warp", "warp_onehot_argmax", "warp_taps", "upsample_flow", "upsample_seg"]

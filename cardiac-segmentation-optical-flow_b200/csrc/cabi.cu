@@ -262,4 +262,14 @@ int cf_sample_points(const float* locs, const float* src, int B, int C, int H, i
     return launch_sample_points(locs, src, B, C, H, W, P, size_h, size_w, mode, out, (cudaStream_t)stream);
 }
 
+int cf_upsample_convex(const float* field, const float* mask, int B, int C, int H, int W, int factor, float scale, float* out,
+                       void* stream) {
+    CF_REQUIRE(field && mask && out, CF_ERR_BAD_ARG, "cf_upsample_convex: null pointer");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_upsample_convex: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    CF_REQUIRE(factor == 8, CF_ERR_UNSUPPORTED, "cf_upsample_convex: factor %d (the reference only has 8)", factor);
+    CF_REQUIRE(aligned16(out), CF_ERR_BAD_ARG, "cf_upsample_convex: out must be 16-byte aligned");
+    CF_REQUIRE(out != field && out != mask, CF_ERR_BAD_ARG, "cf_upsample_convex: out must not alias the inputs");
+    return launch_upsample_convex(field, mask, B, C, H, W, scale, out, (cudaStream_t)stream);
+}
+
 }  // extern "C"

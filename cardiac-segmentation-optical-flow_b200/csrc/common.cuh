@@ -115,6 +115,9 @@ int launch_lookup_taps(const LevelDims& d, const float* coords, int B, int H, in
 int launch_lookup_bwd(const LevelDims& d, const float* coords, const float* go, int B, int H, int W, int L,
                       int r, float* gpyr, cudaStream_t s);
 
+int launch_upsample_convex(const float* field, const float* mask, int B, int C, int H, int W, float scale, float* out,
+                           cudaStream_t s);
+
 // pooled-fmap2 pyramid of the on-the-fly lookup: level l = [B, C, h_l, w_l], 256-byte aligned offsets
 bool fmap_level_dims(int B, int C, int H, int W, int L, LevelDims* d);
 int launch_fmap_pyramid(const float* f2, int B, int C, int H, int W, int L, float* f2pyr, cudaStream_t s);

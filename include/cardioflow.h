@@ -137,6 +137,13 @@ CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* o
 CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int size_h,
                      int size_w, int mode, float* out, void* stream);
 
+/* Convex 8x upsampling (8(f) row 3): replaces `upsample_flow` (SegFlowGaussian.py:846-857, C = 2) and `upsample_seg`
+ * (:860-871, C = 4): out[n,c,8y+i,8x+j] = sum_k softmax_k(mask[n,k*64+i*8+j,y,x]) * scale * field[n,c,y+ky-1,x+kx-1],
+ * k = ky*3+kx, zeros outside.  field [B,C,H,W], mask [B,576,H,W], out [B,C,8H,8W]; the reference passes scale = 8
+ * for both.  Only factor 8 exists in the reference (CF_ERR_UNSUPPORTED otherwise). */
+CF_API int cf_upsample_convex(const float* field, const float* mask, int B, int C, int H, int W, int factor, float scale,
+                       float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -12,6 +12,9 @@ Run in the build container only (``/root/reference`` does not exist on the GPU b
   third-party call site of the reference (``nnMTLTrainerV2Raft.py:97-118``); the reference's own
   ``nnunet/lib/raft_initial.py`` was never committed.
 
+* upsample fixtures:  outputs of the reference's own ``upsample_flow`` / ``upsample_seg`` methods, compiled out of
+  ``/root/reference/nnunet/network_architecture/SegFlowGaussian.py:846-871`` by name (the module's imports are absent).
+
 Every fixture stores its inputs next to the outputs, so the tests do not depend on RNG reproducibility.
 """
 import importlib.util
@@ -134,6 +137,41 @@ def make_corr():
     print("corr_torchvision.npz:", len(out), "arrays")
 
 
+def load_reference_methods(path, names):
+    """Compile single methods of a reference class out of its source file (the module itself cannot be imported: its
+    imports need packages that are absent here).  The methods used here touch only torch / F."""
+    import ast
+    import torch.nn.functional as F
+    src = open(path).read()
+    tree = ast.parse(src)
+    found = {}
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name in names and node.name not in found:
+            ns = {"torch": torch, "F": F}
+            exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
+            found[node.name] = ns[node.name]
+    missing = set(names) - set(found)
+    if missing:
+        raise RuntimeError(f"{path}: methods not found: {sorted(missing)}")
+    return found
+
+
+def make_upsample():
+    ref = load_reference_methods("/root/reference/nnunet/network_architecture/SegFlowGaussian.py",
+                                 ["upsample_flow", "upsample_seg"])
+    out = {}
+    for name, (n, h, w, seed) in {"u_6x5": (2, 6, 5, 4001), "u_12x12": (1, 12, 12, 4002), "u_9x33": (1, 9, 33, 4003)}.items():
+        g = gen(seed)
+        flow = torch.randn(n, 2, h, w, generator=g) * 2.0
+        seg = torch.randn(n, 4, h, w, generator=g)
+        mask = torch.randn(n, 576, h, w, generator=g) * 3.0
+        out[f"{name}.flow"], out[f"{name}.seg"], out[f"{name}.mask"] = flow.numpy(), seg.numpy(), mask.numpy()
+        out[f"{name}.up_flow"] = ref["upsample_flow"](None, flow.clone(), mask.clone()).numpy()
+        out[f"{name}.up_seg"] = ref["upsample_seg"](None, seg.clone(), mask.clone()).numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "upsample_reference.npz"), **out)
+    print("upsample_reference.npz:", len(out), "arrays")
+
+
 if __name__ == "__main__":
     if not os.path.exists(REF_FILE):
         sys.exit("reference not present: fixtures can only be regenerated in the build container")
@@ -141,3 +179,4 @@ if __name__ == "__main__":
     torch.set_num_threads(1)
     make_warp(load_reference_integration())
     make_corr()
+    make_upsample()

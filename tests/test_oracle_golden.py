@@ -117,3 +117,19 @@ def test_live_reference_agrees_with_oracle():
     mine = corr_oracle.CorrBlock(f1, f2)
     coords = corr_oracle.coords_grid(1, 16, 20) + torch.randn(1, 2, 16, 20, generator=g) * 2
     assert torch.equal(tv.index_pyramid(coords), mine(coords))
+
+
+@pytest.mark.parametrize("name", ["u_6x5", "u_12x12", "u_9x33"])
+def test_upsample_restatement_matches_reference_fixture(golden_upsample, name):
+    """oracle/upsample_oracle.py against the outputs of the reference's own upsample_flow / upsample_seg
+    (SegFlowGaussian.py:846-871, frozen by oracle/make_golden.py with one thread): same ATen ops; ATen's softmax / sum split their work by thread count,
+    so agreement is to the last ulp or two (<= 1e-6 relative), not bitwise, when the suite runs multi-threaded."""
+    from oracle import upsample_oracle
+    g = golden_upsample
+    mask = torch.from_numpy(g[f"{name}.mask"])
+    assert rel_err(upsample_oracle.upsample_flow(torch.from_numpy(g[f"{name}.flow"]), mask).numpy(), g[f"{name}.up_flow"]) <= 1e-6
+    assert rel_err(upsample_oracle.upsample_seg(torch.from_numpy(g[f"{name}.seg"]), mask).numpy(), g[f"{name}.up_seg"]) <= 1e-6
+    # convexity: a constant field is reproduced (scaled by 8) away from the zero-padded border
+    const = torch.full((1, 2, 6, 6), 0.25)
+    up = upsample_oracle.upsample_flow(const, torch.randn(1, 576, 6, 6))
+    assert torch.allclose(up[:, :, 8:-8, 8:-8], torch.full_like(up[:, :, 8:-8, 8:-8], 2.0), atol=1e-6)

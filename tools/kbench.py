@@ -128,6 +128,15 @@ if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24", "cfg2h", "cfg2q"):
             us, mn = timeit(lambda i: cf.warp(img[i], flow[i], out=wout[i]), nrot)
             report(f"warp {P}x{cin}x{IH}^2", us, mn, 4 * P * IH * IH * (2 * cin + 2))
 
+if args.cfg in ("cfg2", "cfg4") and want("upsample"):
+    from oracle.upsample_oracle import algorithmic_bytes
+    for cin, fn in ((2, cf.upsample_flow), (4, cf.upsample_seg)):
+        fld = [torch.randn(P, cin, H, W, device=dev) for _ in range(nrot)]
+        msk = [torch.randn(P, 576, H, W, device=dev) for _ in range(nrot)]
+        with torch.no_grad():
+            us, mn = timeit(lambda i: fn(fld[i], msk[i]), nrot)
+        report(f"convex upsample {P}x{cin}x{H}^2 -> {8 * H}^2", us, mn, algorithmic_bytes(P, cin, H, W))
+
 if args.cfg == "cfg3":
     B, IH = 300, 224
     nrot = 2

@@ -12,6 +12,7 @@ HEADER = os.path.join(os.path.dirname(PKG), "include", "cardioflow.h")
 CF_OK, CF_ERR_BAD_ARG, CF_ERR_UNSUPPORTED, CF_ERR_CUDA = 0, -1, -2, -3
 PREC_BF16, PREC_FP32, PREC_AUTO = 0, 1, 2
 MODE_BILINEAR, MODE_NEAREST = 0, 1
+BUILD_ALLOW_TILED = 1
 PRECISIONS = {"bf16": PREC_BF16, "fp32": PREC_FP32, "auto": PREC_AUTO}
 
 _c = ctypes
@@ -25,6 +26,8 @@ _SIGNATURES = {
     "cf_coords_grid": (_I, [_P, _I, _I, _I, _P]),
     "cf_corr_build_workspace_bytes": (_Z, [_I, _I, _I, _I, _I]),
     "cf_corr_build": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _Z, _c.POINTER(_I), _P]),
+    "cf_corr_build_layout": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _Z, _c.POINTER(_I), _c.POINTER(_c.c_uint), _P]),
+    "cf_corr_lookup_layout": (_I, [_P, _P, _I, _I, _I, _I, _I, _c.c_uint, _P, _P]),
     "cf_corr_pool": (_I, [_P, _I, _I, _I, _I, _I, _P]),
     "cf_corr_lookup": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "cf_corr_lookup_taps": (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),

@@ -56,7 +56,7 @@ class _CorrBuild(torch.autograd.Function):
     """(fmap1, fmap2) -> packed pyramid.  a2 + a3 of SURVEY.md 8(a)."""
 
     @staticmethod
-    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None):
+    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None, allow_tiled=False):
         B, C, H, W = fmap1.shape
         lib = _cabi.lib()
         f1, f2 = _cabi.f32c(fmap1), _cabi.f32c(fmap2)
@@ -68,12 +68,16 @@ class _CorrBuild(torch.autograd.Function):
         else:
             pyramid = pyramid.view(-1)[:nfloats]
         used = _cabi.ctypes.c_int(-1)
+        tiled = _cabi.ctypes.c_uint(0)
         ws_bytes = lib.cf_corr_build_workspace_bytes(B, C, H, W, precision)
         ws = _workspace(f1.device, ws_bytes)
         with torch.cuda.device(f1.device):
-            _cabi.check(lib.cf_corr_build(f1.data_ptr(), f2.data_ptr(), B, C, H, W, num_levels, precision,
-                                          pyramid.data_ptr(), ws.data_ptr() if ws is not None else None, ws_bytes,
-                                          _cabi.ctypes.byref(used), _cabi.stream()), "cf_corr_build")
+            _cabi.check(lib.cf_corr_build_layout(f1.data_ptr(), f2.data_ptr(), B, C, H, W, num_levels, precision,
+                                                 _cabi.BUILD_ALLOW_TILED if allow_tiled else 0, pyramid.data_ptr(),
+                                                 ws.data_ptr() if ws is not None else None, ws_bytes,
+                                                 _cabi.ctypes.byref(used), _cabi.ctypes.byref(tiled), _cabi.stream()),
+                        "cf_corr_build_layout")
+        _CorrBuild.last_tiled_mask = tiled.value
         ctx.save_for_backward(f1, f2)
         ctx.meta = (B, C, H, W, num_levels)
         ctx.used_precision = used.value
@@ -92,7 +96,7 @@ class _CorrBuild(torch.autograd.Function):
             _cabi.check(lib.cf_corr_pool_bwd(g.data_ptr(), B, H, W, L, s), "cf_corr_pool_bwd")
             _cabi.check(lib.cf_corr_volume_bwd(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W,
                                                gf1.data_ptr(), gf2.data_ptr(), s), "cf_corr_volume_bwd")
-        return gf1, gf2, None, None, None
+        return gf1, gf2, None, None, None, None
 
 
 class _CorrLookup(torch.autograd.Function):
@@ -100,7 +104,7 @@ class _CorrLookup(torch.autograd.Function):
     (the reference detaches them before every lookup, SegFlowGaussian.py:933)."""
 
     @staticmethod
-    def forward(ctx, pyramid, coords, meta, out=None):
+    def forward(ctx, pyramid, coords, meta, out=None, tiled_mask=0):
         B, H, W, L, r = meta
         c = _cabi.f32c(coords)
         shape = (B, L * (2 * r + 1) ** 2, H, W)
@@ -109,8 +113,8 @@ class _CorrLookup(torch.autograd.Function):
         elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
             raise ValueError(f"out must be a contiguous fp32 tensor of shape {shape}")
         with torch.cuda.device(pyramid.device):
-            _cabi.check(_cabi.lib().cf_corr_lookup(pyramid.data_ptr(), c.data_ptr(), B, H, W, L, r, out.data_ptr(),
-                                                   _cabi.stream()), "cf_corr_lookup")
+            _cabi.check(_cabi.lib().cf_corr_lookup_layout(pyramid.data_ptr(), c.data_ptr(), B, H, W, L, r, tiled_mask,
+                                                          out.data_ptr(), _cabi.stream()), "cf_corr_lookup_layout")
         ctx.save_for_backward(c)
         ctx.meta = meta
         ctx.numel = pyramid.numel()
@@ -125,7 +129,7 @@ class _CorrLookup(torch.autograd.Function):
         with torch.cuda.device(go.device):
             _cabi.check(_cabi.lib().cf_corr_lookup_bwd(c.data_ptr(), go.data_ptr(), B, H, W, L, r, g.data_ptr(),
                                                        _cabi.stream()), "cf_corr_lookup_bwd")
-        return g, None, None, None
+        return g, None, None, None, None
 
 
 class CorrBlock:
@@ -171,11 +175,34 @@ class CorrBlock:
                                                       self._f2_pyramid.data_ptr(), _cabi.stream()), "cf_fmap_pyramid_build")
             self.used_precision = "fp32"
             self._pyramid = None
-            self.corr_pyramid = None
+            self._tiled_mask = 0
             return
-        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer)
+        # Inference only: the tensor-core builder may store level 0 as 4x4 tiles (fewer DRAM atoms per lookup window).  With
+        # autograd on, the pyramid stays row-major: the backward kernels and any user arithmetic on corr_pyramid expect it.
+        needs_grad = torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)
+        allow_tiled = not needs_grad and os.environ.get("CARDIOFLOW_TILED", "1") != "0"
+        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer, allow_tiled)
         self.used_precision = {0: "bf16", 1: "fp32"}.get(getattr(_CorrBuild, "last_used_precision", -1), "?")
-        self.corr_pyramid = _level_views(self._pyramid, B, H, W, num_levels)
+        self._tiled_mask = getattr(_CorrBuild, "last_tiled_mask", 0) if allow_tiled else 0
+        self._views = None
+
+    @property
+    def corr_pyramid(self):
+        """torchvision's ``corr_pyramid``: list of [B*H*W, 1, h_l, w_l] tensors.  Zero-copy views of the packed buffer for
+        row-major levels; a level stored as 4x4 tiles is returned as an un-tiled copy."""
+        if self._pyramid is None:
+            return None
+        if self._views is None:
+            B, H, W, L, _ = self._meta
+            views = _level_views(self._pyramid, B, H, W, L)
+            for lvl in range(L):
+                if (self._tiled_mask >> lvl) & 1:
+                    n, _, h, w = views[lvl].shape
+                    views[lvl] = views[lvl].reshape(n, h // 4, w // 4, 4, 4).permute(0, 1, 3, 2, 4).reshape(n, 1, h, w)
+            if self._tiled_mask:
+                return views           # copies: not cached (the packed buffer may be a caller-owned, reused buffer)
+            self._views = views
+        return self._views
 
     @classmethod
     def from_pyramid(cls, levels, radius=4):
@@ -194,8 +221,9 @@ class CorrBlock:
         self._meta = (B, H, W, L, radius)
         self._pyramid = packed
         self.used_precision = "external"
-        self.corr_pyramid = _level_views(packed, B, H, W, L)
-        for view, src in zip(self.corr_pyramid, levels):
+        self._tiled_mask = 0
+        self._views = _level_views(packed, B, H, W, L)
+        for view, src in zip(self._views, levels):
             view.copy_(src.reshape(view.shape))
         return self
 
@@ -206,7 +234,7 @@ class CorrBlock:
         if self.on_the_fly:
             return self._lookup_on_the_fly(coords, out)
         _cabi.require_cuda(self._pyramid, coords)
-        return _CorrLookup.apply(self._pyramid, coords, self._meta, out)
+        return _CorrLookup.apply(self._pyramid, coords, self._meta, out, self._tiled_mask)
 
     def _lookup_on_the_fly(self, coords, out=None):
         B, H, W, L, r = self._meta

@@ -92,6 +92,17 @@ size_t cf_corr_build_workspace_bytes(int B, int C, int H, int W, int precision) 
 
 int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
                   float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision, void* stream) {
+    return cf_corr_build_layout(f1, f2, B, C, H, W, L, precision, 0, pyramid, workspace, workspace_bytes, used_precision,
+                                nullptr, stream);
+}
+
+int cf_corr_build_layout(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision, int flags,
+                         float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision,
+                         unsigned* tiled_mask, void* stream) {
+    if (tiled_mask) *tiled_mask = 0;
+    CF_REQUIRE((flags & ~CF_BUILD_ALLOW_TILED) == 0, CF_ERR_BAD_ARG, "cf_corr_build_layout: unknown flags 0x%x", flags);
+    CF_REQUIRE(!(flags & CF_BUILD_ALLOW_TILED) || tiled_mask, CF_ERR_BAD_ARG,
+               "cf_corr_build_layout: CF_BUILD_ALLOW_TILED needs tiled_mask to report the layout");
     CF_REQUIRE(f1 && f2 && pyramid, CF_ERR_BAD_ARG, "cf_corr_build: null pointer");
     CF_REQUIRE(C > 0, CF_ERR_BAD_ARG, "cf_corr_build: C must be positive");
     CF_REQUIRE(((uintptr_t)pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_build: pyramid must be 256-byte aligned");
@@ -110,7 +121,8 @@ int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, 
         // the GEMM fuses as many pooled levels into its epilogue as the shape allows (none .. all)
         if (corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2)) {
             int done = 1;
-            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, levels, L, workspace, workspace_bytes, &done, s);
+            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, levels, L, workspace, workspace_bytes, &done,
+                                     (flags & CF_BUILD_ALLOW_TILED) != 0, tiled_mask, s);
             if (rc) return rc;
             used = CF_PREC_BF16;
             from_level = done - 1;
@@ -140,13 +152,19 @@ int cf_corr_pool(float* pyramid, int B, int H, int W, int L, int from_level, voi
 
 int cf_corr_lookup(const float* pyramid, const float* coords, int B, int H, int W, int L, int r, float* out,
                    void* stream) {
+    return cf_corr_lookup_layout(pyramid, coords, B, H, W, L, r, 0u, out, stream);
+}
+
+int cf_corr_lookup_layout(const float* pyramid, const float* coords, int B, int H, int W, int L, int r, unsigned tiled_mask,
+                          float* out, void* stream) {
     CF_REQUIRE(pyramid && coords && out, CF_ERR_BAD_ARG, "cf_corr_lookup: null pointer");
     CF_REQUIRE(r >= 1 && r <= CF_MAX_RADIUS, CF_ERR_UNSUPPORTED, "cf_corr_lookup: radius %d not in [1,%d]", r, CF_MAX_RADIUS);
     CF_REQUIRE(((uintptr_t)pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_lookup: pyramid must be 256-byte aligned");
     LevelDims d;
     int rc = check_corr_shape(B, H, W, L, &d);
     if (rc) return rc;
-    return launch_lookup(pyramid, d, coords, B, H, W, L, r, out, (cudaStream_t)stream);
+    CF_REQUIRE(L >= 32 || (tiled_mask >> L) == 0, CF_ERR_BAD_ARG, "cf_corr_lookup_layout: tiled_mask 0x%x names levels >= %d", tiled_mask, L);
+    return launch_lookup(pyramid, d, coords, B, H, W, L, r, out, tiled_mask, (cudaStream_t)stream);
 }
 
 int cf_corr_lookup_taps(const float* coords, int B, int H, int W, int L, int r, float* taps, int32_t* idx,

@@ -102,6 +102,7 @@ int launch_corr_simt(const float* f1, const float* f2, int B, int C, int HW, flo
 // returns CF_ERR_UNSUPPORTED (without touching the stream) when the shape does not fit the TMA/UMMA tiling
 int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* const* levels, int L,
                         void* workspace, size_t ws_bytes, int* levels_done /* levels written by the GEMM */,
+                        bool allow_tiled, unsigned* tiled_mask /* out: bit l set when level l was written as 4x4 tiles */,
                         cudaStream_t s);
 size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W);
 bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool);
@@ -109,7 +110,7 @@ int launch_corr_volume_bwd(const float* f1, const float* f2, const float* gcorr,
                            float* gf1, float* gf2, cudaStream_t s);
 
 int launch_lookup(const float* pyramid, const LevelDims& d, const float* coords, int B, int H, int W, int L,
-                  int r, float* out, cudaStream_t s);
+                  int r, float* out, unsigned tiled_mask /* bit l: level l stored as 4x4 tiles */, cudaStream_t s);
 int launch_lookup_taps(const LevelDims& d, const float* coords, int B, int H, int W, int L, int r, float* taps,
                        int32_t* idx, cudaStream_t s);
 int launch_lookup_bwd(const LevelDims& d, const float* coords, const float* go, int B, int H, int W, int L,

@@ -59,6 +59,7 @@ struct GemmParams {
     unsigned long long* ts;  // bring-up only: per-role timestamps of CTA `ts_cta` (null in production)
     int ts_cta;
     float* dbg;          // bring-up only: raw accumulators + smem operand dump of CTA 0 (null in production)
+    int tile_l0;         // W == 32 epilogue: write level 0 as 4x4 tiles (CF_LAYOUT_TILED4)
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -335,9 +336,26 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 if (ep_tid == 0) tma_store_wait_read<0>();   // the previous tile's stores have read their buffers
                 epi_bar_sync();
                 if (ep_tid == 0) CF_TS(66 + 4 * t);
+                // Tiled level 0: the tile's 128 accumulators are image rows 4k..4k+3 = one row of eight 4x4 tiles, i.e. the same
+                // 128-float range of the query's image in both layouts; only the order inside it changes.  16 B piece j of
+                // chunk c holds row (j & 3) of tile 2c + (j >> 2): a static permutation of register indices, no extra work.
+                if (P.tile_l0) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const uint32_t dst = S.epi(c) + (uint32_t)row * 128u;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float* src = v + (j & 3) * 32 + (2 * c + (j >> 2)) * 4;
+                            const uint32_t addr = dst + (uint32_t)((j ^ (row & 7)) << 4);
+                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(src[0]), "f"(src[1]),
+                                         "f"(src[2]), "f"(src[3]) : "memory");
+                        }
+                    }
+                }
 #pragma unroll
                 for (int c = 0; c < 5; ++c) {
                     if (c == 4 && P.level1 == nullptr) break;
+                    if (c < 4 && P.tile_l0) continue;
                     const float* src = c < 4 ? v + 32 * c : l1;
                     const uint32_t dst = S.epi(c) + (uint32_t)row * 128u;
 #pragma unroll
@@ -548,7 +566,9 @@ size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W) {
 }
 
 int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, int W, float* const* levels, int L,
-                        void* workspace, size_t ws_bytes, int* levels_done, cudaStream_t s) {
+                        void* workspace, size_t ws_bytes, int* levels_done, bool allow_tiled, unsigned* tiled_mask,
+                        cudaStream_t s) {
+    if (tiled_mask) *tiled_mask = 0;
     const int HW = H * W;
     float* level0 = levels[0];
     float* level1 = (L > 1 && fused_bn(H, W) != 0) ? levels[1] : nullptr;
@@ -590,6 +610,9 @@ int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, i
     if (w32 && L > 2) P.level2 = levels[2];
     if (w32 && L > 3 && (H % 8) == 0 && (tiles_per % 2) == 0 && P.n_tiles % split == 0) P.level3 = levels[3];
     *levels_done = P.level3 ? 4 : (P.level2 ? 3 : (level1 ? 2 : 1));
+    // level 0 as 4x4 tiles (fewer DRAM atoms per lookup window): only the register-resident epilogue can reorder for free
+    P.tile_l0 = (w32 && allow_tiled && tiled_mask) ? 1 : 0;
+    if (P.tile_l0) *tiled_mask = 1u;
 
     CUtensorMap tmA, tmB, tmC;
     int rc;

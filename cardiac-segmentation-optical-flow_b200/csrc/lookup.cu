@@ -62,6 +62,7 @@ struct LookupParams {
     int HW;
     int L;
     int lshift;     // log2(L) when L is a power of two, else -1
+    unsigned tiled; // bit l: level l is stored as 4x4 tiles (cardioflow.h: CF_LAYOUT_TILED4)
 };
 
 // flags a lane publishes about its query (shuffled to the lanes that stage its window)
@@ -108,7 +109,9 @@ __device__ __forceinline__ int win_base(int q) { return q * Geo<R>::QP + 4 * (q 
 // Stage the windows of the CTA's 32 queries.  A pass = one window row of 8 queries x 4 sixteen-byte chunks; warp w
 // takes rows w, w+NW, ...  VEC: level width is a multiple of 4, chunks are 16 B-aligned in global memory (window
 // column a <-> image column (ax & ~3) + a); otherwise chunks start at the anchor column and are copied element-wise.
-template <int R, int NW, bool VEC>
+// TILED (implies VEC): the level image is stored as 4x4 tiles (64 B each, tile-row-major), so the 16 B chunk (row y, columns
+// gx..gx+3) lives at ((y >> 2) * (wl / 4) + gx / 4) * 16 + (y & 3) * 4 words and the four rows of a tile share one DRAM atom.
+template <int R, int NW, bool VEC, bool TILED = false>
 __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __restrict__ img0, int hl, int wl, int w,
                                               int lane, int ax, int ay, unsigned flags) {
     using G = Geo<R>;
@@ -132,15 +135,18 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
         // the one row only a flipped floor can reach
         const int skip = (q_fl & kNomY) ? ((q_fl & kLoY) ? 0 : PR - 1) : -1;
         const bool col_in = (unsigned)gx < (unsigned)wl;              // VEC: chunks are entirely in or out
-        const char* gq = reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)(q_ay + w) * wl + gx));
+        const char* gq = TILED ? reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)gx * 4))
+                               : reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)(q_ay + w) * wl + gx));
         const unsigned row_bytes = (unsigned)(NW * wl) * 4u;
+        const int tile_row_bytes = wl * 16;                             // TILED: bytes of one row of tiles
         const uint32_t sq = win_s + (uint32_t)(win_base<R>(src) + w * PC + 4 * ch) * 4u;
 #pragma unroll
         for (int k = 0; k < RPW; ++k) {
             const int r = w + NW * k;
             if (ch_need && r < PR && r != skip) {
                 const bool row_in = (unsigned)(q_ay + r) < (unsigned)hl;
-                const char* gp = gq + (unsigned)k * row_bytes;
+                const int yrow = q_ay + r;
+                const char* gp = TILED ? gq + ((yrow >> 2) * tile_row_bytes + (yrow & 3) * 16) : gq + (unsigned)k * row_bytes;
                 const uint32_t d = sq + (uint32_t)(NW * k * PC) * 4u;
                 if (VEC) {
                     const bool in = row_in && col_in;
@@ -209,7 +215,8 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
         const unsigned flags = (dead ? kDead : 0u) | (nom_x ? kNomX : 0u) | (nom_y ? kNomY : 0u) | (lo_x ? kLoX : 0u) |
                                (lo_y ? kLoY : 0u);
         const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
-        if (vec) stage_windows<R, NW, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
+        if ((P.tiled >> l) & 1u) stage_windows<R, NW, true, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
+        else if (vec) stage_windows<R, NW, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
         else stage_windows<R, NW, false>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
     }
 
@@ -343,7 +350,8 @@ __global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__
         const unsigned flags = (dead ? kDead : 0u) | (nom_x ? kNomX : 0u) | (nom_y ? kNomY : 0u) | (lo_x ? kLoX : 0u) |
                                (lo_y ? kLoY : 0u);
         const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
-        if (vec) stage_windows<R, 1, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
+        if ((P.tiled >> l) & 1u) stage_windows<R, 1, true, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
+        else if (vec) stage_windows<R, 1, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
         else stage_windows<R, 1, false>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
     }
     // x taps (registers) while the copies are in flight
@@ -512,9 +520,13 @@ LookupParams make_params(const float* pyramid, const LevelDims& d, const float* 
 }  // namespace
 
 int launch_lookup(const float* pyramid, const LevelDims& d, const float* coords, int B, int H, int W, int L, int r,
-                  float* out, cudaStream_t s) {
+                  float* out, unsigned tiled_mask, cudaStream_t s) {
     LookupParams P = make_params(pyramid, d, coords, B, H, W, L);
     P.out = out;
+    for (int l = 0; l < L; ++l)
+        if (((tiled_mask >> l) & 1u) && ((d.h[l] | d.w[l]) & 3))
+            return fail(CF_ERR_BAD_ARG, "lookup: level %d (%dx%d) cannot be 4x4-tiled", l, d.h[l], d.w[l]);
+    P.tiled = tiled_mask;
     switch (r) {
         case 1: return launch_lookup_r<1>(P, s);
         case 2: return launch_lookup_r<2>(P, s);

@@ -74,6 +74,18 @@ CF_API size_t cf_corr_build_workspace_bytes(int B, int C, int H, int W, int prec
 CF_API int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
                   float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision, void* stream);
 
+/* Layout-aware variants.  With CF_BUILD_ALLOW_TILED the builder may store pyramid levels as 4x4 tiles (CF_LAYOUT_TILED4:
+ * element (y, x) of a query's h_l x w_l image at ((y/4) * (w_l/4) + x/4) * 16 + (y%4) * 4 + x%4; same level offsets and
+ * sizes) -- a lookup window then touches ~10 instead of ~16 DRAM atoms.  `tiled_mask` receives bit l = 1 for every level
+ * written that way (0 = torchvision's row-major layout); pass it unchanged to cf_corr_lookup_layout.  Every other entry
+ * point (pooling, backward passes) works on row-major pyramids only: keep flags = 0 for pyramids they will see. */
+#define CF_BUILD_ALLOW_TILED 1
+CF_API int cf_corr_build_layout(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision, int flags,
+                         float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision,
+                         unsigned* tiled_mask, void* stream);
+CF_API int cf_corr_lookup_layout(const float* pyramid, const float* coords, int B, int H, int W, int L, int r,
+                          unsigned tiled_mask, float* out, void* stream);
+
 /* Rebuild levels from_level+1 .. L-1 from level from_level (F.avg_pool2d(x, 2, stride=2), floor mode). */
 CF_API int cf_corr_pool(float* pyramid, int B, int H, int W, int L, int from_level, void* stream);
 

@@ -190,3 +190,31 @@ def test_full_size_properties_cfg4():
     ref = corr_oracle.CorrBlock(f1[:1].cpu(), f2[:1].cpu())
     want = ref(coords[:1].cpu()).numpy()
     assert np.abs(blk(coords)[:1].cpu().numpy() - want).max() <= 2e-5 * np.abs(want).max()
+
+
+def test_tiled_level0_is_invisible(monkeypatch):
+    """The tensor-core builder stores level 0 as 4x4 tiles when no gradient is needed (cf_corr_build_layout /
+    cf_corr_lookup_layout).  Nothing observable may change: pyramid values and every lookup are bit-identical to the
+    row-major build, `corr_pyramid` still has torchvision's shapes, and autograd keeps the row-major layout."""
+    g = torch.Generator().manual_seed(77)
+    f1, f2 = torch.randn(3, 256, 32, 32, generator=g).to(DEV), torch.randn(3, 256, 32, 32, generator=g).to(DEV)
+    coords = [(cf.coords_grid(3, 32, 32, device=DEV) + s * torch.randn(3, 2, 32, 32, generator=g).to(DEV)) for s in (0.0, 0.7, 3.0, 40.0)]
+    monkeypatch.setenv("CARDIOFLOW_TILED", "0")
+    plain = cf.CorrBlock(f1, f2, precision="bf16")
+    assert plain._tiled_mask == 0
+    monkeypatch.setenv("CARDIOFLOW_TILED", "1")
+    tiled = cf.CorrBlock(f1, f2, precision="bf16")
+    assert tiled._tiled_mask == 1, "W = 32 tensor-core build is expected to tile level 0"
+    for a, b in zip(plain.corr_pyramid, tiled.corr_pyramid):
+        assert a.shape == b.shape and torch.equal(a, b)
+    for c in coords:
+        assert torch.equal(plain(c), tiled(c))
+    # raw storage of level 0 really is tiled: element (y, x) of image 5 sits at tile-major position
+    raw = tiled._pyramid[:3 * 1024 * 1024].view(3 * 1024, 8, 8, 4, 4)
+    assert float(raw[5, 2, 3, 1, 2]) == float(plain.corr_pyramid[0][5, 0, 2 * 4 + 1, 3 * 4 + 2])
+    # with autograd the layout stays row-major and gradients flow
+    fa, fb = f1.clone().requires_grad_(), f2.clone().requires_grad_()
+    blk = cf.CorrBlock(fa, fb, precision="bf16")
+    assert blk._tiled_mask == 0
+    blk(coords[1]).mean().backward()
+    assert fa.grad is not None and torch.isfinite(fa.grad).all()

@@ -7,7 +7,7 @@ name carries a hyphen and cannot be imported directly).
 """
 from .corr import CorrBlock, coords_grid, lookup_taps
 from .upsample import upsample_flow, upsample_seg
-from .warp import SpatialTransformer, SpatialTransformerContour, VecInt, warp, warp_onehot_argmax, warp_taps
+from .warp import SpatialTransformer, SpatialTransformerContour, VecInt, utils_warp, warp, warp_onehot_argmax, warp_taps
 
 __all__ = ["CorrBlock", "coords_grid", "lookup_taps", "SpatialTransformer", "SpatialTransformerContour", "VecInt",
-           "warp", "warp_onehot_argmax", "warp_taps", "upsample_flow", "upsample_seg"]
+           "warp", "warp_onehot_argmax", "warp_taps", "upsample_flow", "upsample_seg", "utils_warp"]

@@ -280,6 +280,13 @@ int cf_sample_points(const float* locs, const float* src, int B, int C, int H, i
     return launch_sample_points(locs, src, B, C, H, W, P, size_h, size_w, mode, out, (cudaStream_t)stream);
 }
 
+int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, void* stream) {
+    CF_REQUIRE(flow && src && out, CF_ERR_BAD_ARG, "cf_warp2d_xy: null pointer");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_warp2d_xy: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    CF_REQUIRE(out != src && out != flow, CF_ERR_BAD_ARG, "cf_warp2d_xy: out must not alias the inputs");
+    return launch_warp2d_xy(flow, src, B, C, H, W, out, (cudaStream_t)stream);
+}
+
 int cf_upsample_convex(const float* field, const float* mask, int B, int C, int H, int W, int factor, float scale, float* out,
                        void* stream) {
     CF_REQUIRE(field && mask && out, CF_ERR_BAD_ARG, "cf_upsample_convex: null pointer");

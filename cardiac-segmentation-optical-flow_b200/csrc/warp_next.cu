@@ -190,4 +190,42 @@ int launch_sample_points(const float* locs, const float* src, int B, int C, int 
     return CF_OK;
 }
 
+// ---------------------------------------------------------------------------------------------- lib/utils.warp
+// SURVEY.md 8(f) row 4 (second half): /root/reference/nnunet/lib/utils.py:29-59 `warp(x, flo)`, used at
+// network_architecture/SegFlowGaussian.py:1044.  Unlike SpatialTransformer: flow channel 0 displaces COLUMNS, channel 1
+// rows; n = 2*(p + f)/max(S-1, 1) - 1; grid_sample with its defaults (bilinear, zeros, align_corners=False), whose
+// un-normalisation is ((n + 1) * S - 1) / 2 -- coordinates land half a pixel off the align_corners=True warp.
+// Same fp32 operation order as the reference -> bit-exact taps.  lane = column, blockIdx.y = row, blockIdx.z = item.
+namespace {
+__device__ __forceinline__ float utils_warp_coord(float p, float d1 /* max(S-1,1) */, float size) {
+    const float n = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, p), d1), 1.0f);
+    return __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(n, 1.0f), size), 1.0f), 0.5f);
+}
+
+__global__ void __launch_bounds__(128) warp2d_xy_kernel(const float* __restrict__ flow, const float* __restrict__ src,
+                                                        float* __restrict__ out, int B, int C, int H, int W) {
+    const int x = blockIdx.x * 128 + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const unsigned HW = (unsigned)(H * W), pix = (unsigned)y * (unsigned)W + (unsigned)x;
+    const float dx1 = (float)max(W - 1, 1), dy1 = (float)max(H - 1, 1);
+    for (unsigned b = blockIdx.z; b < (unsigned)B; b += gridDim.z) {
+        const float* fl = flow + (size_t)b * 2 * HW + pix;
+        const float ux = utils_warp_coord(__fadd_rn((float)x, __ldg(fl)), dx1, (float)W);
+        const float uy = utils_warp_coord(__fadd_rn((float)y, __ldg(fl + HW)), dy1, (float)H);
+        const Tap tp = make_tap(uy, ux);
+        const float* img = src + (size_t)b * C * HW;
+        float* o = out + (size_t)b * C * HW + pix;
+        for (int c = 0; c < C; ++c, img += HW, o += HW) *o = sample_bilinear(img, H, W, tp);
+    }
+}
+}  // namespace
+
+int launch_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, cudaStream_t s) {
+    if ((long)H * W >= (1L << 30) || H > 65535) return fail(CF_ERR_UNSUPPORTED, "warp2d_xy: image of %dx%d pixels too large", H, W);
+    const dim3 grid((unsigned)cdiv(W, 128), (unsigned)H, (unsigned)(B < 65535 ? B : 65535));
+    warp2d_xy_kernel<<<grid, 128, 0, s>>>(flow, src, out, B, C, H, W);
+    CF_CHECK_LAUNCH("warp2d_xy_kernel");
+    return CF_OK;
+}
+
 }  // namespace cf

@@ -79,6 +79,23 @@ def warp_onehot_argmax(flow, label, num_classes=4):
     return out
 
 
+def utils_warp(x, flo):
+    """Drop-in for ``nnunet.lib.utils.warp(x, flo)`` (/root/reference/nnunet/lib/utils.py:29-59, called at
+    SegFlowGaussian.py:1044): x [B,C,H,W], flo [B,2,H,W] with channel 0 = x displacement; grid_sample defaults
+    (bilinear, zeros, align_corners=False).  Forward only."""
+    _check_pair(flo, x)
+    _cabi.require_cuda(x, flo)
+    if torch.is_grad_enabled() and (x.requires_grad or flo.requires_grad):
+        raise NotImplementedError("utils_warp: the CUDA path is forward-only; call it under torch.no_grad()")
+    f, src = _cabi.f32c(flo), _cabi.f32c(x)
+    B, C, H, W = src.shape
+    out = torch.empty_like(src)
+    with torch.cuda.device(src.device):
+        _cabi.check(_cabi.lib().cf_warp2d_xy(f.data_ptr(), src.data_ptr(), B, C, H, W, out.data_ptr(), _cabi.stream()),
+                    "cf_warp2d_xy")
+    return out
+
+
 def warp_taps(flow):
     """Parity hook: [B,2,H,W] sampling coordinates (ch0 = row, ch1 = column) the warp kernel derives."""
     _cabi.require_cuda(flow)

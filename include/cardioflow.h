@@ -149,6 +149,11 @@ CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* o
 CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int size_h,
                      int size_w, int mode, float* out, void* stream);
 
+/* lib/utils.warp (8(f) row 4): replaces `warp(x, flo)` of nnunet/lib/utils.py:29-59 (call site SegFlowGaussian.py:1044).
+ * flow [B,2,H,W] with ch0 displacing COLUMNS and ch1 rows; n = 2*(p+f)/max(S-1,1) - 1; grid_sample defaults:
+ * bilinear, zero padding, align_corners=False.  src / out [B,C,H,W]. */
+CF_API int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, void* stream);
+
 /* Convex 8x upsampling (8(f) row 3): replaces `upsample_flow` (SegFlowGaussian.py:846-857, C = 2) and `upsample_seg`
  * (:860-871, C = 4): out[n,c,8y+i,8x+j] = sum_k softmax_k(mask[n,k*64+i*8+j,y,x]) * scale * field[n,c,y+ky-1,x+kx-1],
  * k = ky*3+kx, zeros outside.  field [B,C,H,W], mask [B,576,H,W], out [B,C,8H,8W]; the reference passes scale = 8

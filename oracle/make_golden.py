@@ -156,6 +156,35 @@ def load_reference_methods(path, names):
     return found
 
 
+def make_utils_warp():
+    """lib/utils.py:29-59 `warp`, compiled out of the reference file; its hard-coded `grid.cuda()` is made a no-op for
+    the duration of the call (this container has no GPU; on CPU the function is otherwise unchanged)."""
+    import torch.nn as nn
+    import ast
+    path = "/root/reference/nnunet/lib/utils.py"
+    tree = ast.parse(open(path).read())
+    node = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "warp")
+    ns = {"torch": torch, "nn": nn}
+    exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
+    out = {}
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        for name, (b, c, h, w, amp, seed) in {"uw_24": (2, 3, 24, 24, 2.0, 5001), "uw_17x40": (1, 2, 17, 40, 4.0, 5002),
+                                              "uw_oob_16": (1, 1, 16, 16, 25.0, 5003), "uw_zero_12": (1, 2, 12, 12, 0.0, 5004)}.items():
+            g = gen(seed)
+            x = torch.rand(b, c, h, w, generator=g)
+            flo = torch.randn(b, 2, h, w, generator=g) * amp
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                res = ns["warp"](x.clone(), flo.clone())
+            out[f"{name}.x"], out[f"{name}.flo"], out[f"{name}.out"] = x.numpy(), flo.numpy(), res.numpy()
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    np.savez_compressed(os.path.join(GOLDEN, "utils_warp_reference.npz"), **out)
+    print("utils_warp_reference.npz:", len(out), "arrays")
+
+
 def make_upsample():
     ref = load_reference_methods("/root/reference/nnunet/network_architecture/SegFlowGaussian.py",
                                  ["upsample_flow", "upsample_seg"])
@@ -180,3 +209,4 @@ if __name__ == "__main__":
     make_warp(load_reference_integration())
     make_corr()
     make_upsample()
+    make_utils_warp()

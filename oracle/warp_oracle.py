@@ -86,3 +86,16 @@ def warp_onehot_argmax(flow, label, num_classes=4):
 def warp_algorithmic_bytes(b, c, h, w):
     """src read + out write + flow read."""
     return 4 * b * h * w * (2 * c + 2)
+
+
+def utils_warp(x, flo):
+    """/root/reference/nnunet/lib/utils.py:29-59 `warp(x, flo)` without its hard-coded ``.cuda()``: flow channel 0
+    displaces columns, channel 1 rows; ``grid_sample`` with its defaults (bilinear, zeros, align_corners=False)."""
+    B, C, H, W = x.size()
+    xx = torch.arange(0, W).view(1, -1).repeat(H, 1).view(1, 1, H, W).repeat(B, 1, 1, 1)
+    yy = torch.arange(0, H).view(-1, 1).repeat(1, W).view(1, 1, H, W).repeat(B, 1, 1, 1)
+    vgrid = torch.cat((xx, yy), 1).float() + flo
+    vgrid[:, 0, :, :] = 2.0 * vgrid[:, 0, :, :].clone() / max(W - 1, 1) - 1.0
+    vgrid[:, 1, :, :] = 2.0 * vgrid[:, 1, :, :].clone() / max(H - 1, 1) - 1.0
+    return torch.nn.functional.grid_sample(x, vgrid.permute(0, 2, 3, 1), mode="bilinear", padding_mode="zeros",
+                                           align_corners=False)

@@ -39,6 +39,12 @@ def golden_upsample():
     return np.load(os.path.join(GOLDEN, "upsample_reference.npz"))
 
 
+@pytest.fixture(scope="session")
+def golden_utils_warp():
+    return np.load(os.path.join(GOLDEN, "utils_warp_reference.npz"))
+
+
+UTILS_WARP_CASES = ["uw_24", "uw_17x40", "uw_oob_16", "uw_zero_12"]
 UPSAMPLE_CASES = ["u_6x5", "u_12x12", "u_9x33"]
 WARP_CASES = ["zero_24", "integer_32x40", "half_16", "noise_48", "smooth_64x48", "oob_20"]
 CORR_CASES = ["c16_16x16", "c8_24x24", "c32_16x24"]

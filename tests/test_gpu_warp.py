@@ -110,3 +110,26 @@ def test_full_size_properties_cfg3():
     sub = slice(0, 2)
     ref = warp_oracle.SpatialTransformer((224, 224))(flow[sub].cpu(), src[sub].cpu())
     assert rel_err(st(flow[sub], src[sub]).cpu().numpy(), ref.numpy()) <= 1e-5
+
+
+@pytest.mark.parametrize("name", ["uw_24", "uw_17x40", "uw_oob_16", "uw_zero_12"])
+def test_utils_warp_golden(golden_utils_warp, name):
+    """cf_warp2d_xy (lib/utils.py:29-59 `warp`, align_corners=False, flow ch0 = x) against the reference's own outputs."""
+    import cardioflow_b200 as cf
+    g = golden_utils_warp
+    with torch.no_grad():
+        got = cf.utils_warp(torch.from_numpy(g[f"{name}.x"]).cuda(), torch.from_numpy(g[f"{name}.flo"]).cuda())
+    assert rel_err(got.cpu().numpy(), g[f"{name}.out"]) <= 1e-5
+
+
+def test_utils_warp_full_size_against_oracle():
+    import cardioflow_b200 as cf
+    from oracle import warp_oracle
+    gen = torch.Generator().manual_seed(9)
+    x = torch.rand(4, 5, 224, 224, generator=gen)
+    flo = torch.randn(4, 2, 224, 224, generator=gen) * 3
+    with torch.no_grad():
+        got = cf.utils_warp(x.cuda(), flo.cuda())
+    assert rel_err(got.cpu().numpy(), warp_oracle.utils_warp(x, flo).numpy()) <= 1e-5
+    with pytest.raises(RuntimeError):
+        cf.utils_warp(x, flo)          # CPU tensors: no fallback

@@ -133,3 +133,13 @@ def test_upsample_restatement_matches_reference_fixture(golden_upsample, name):
     const = torch.full((1, 2, 6, 6), 0.25)
     up = upsample_oracle.upsample_flow(const, torch.randn(1, 576, 6, 6))
     assert torch.allclose(up[:, :, 8:-8, 8:-8], torch.full_like(up[:, :, 8:-8, 8:-8], 2.0), atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["uw_24", "uw_17x40", "uw_oob_16", "uw_zero_12"])
+def test_utils_warp_restatement_matches_reference_fixture(golden_utils_warp, name):
+    """oracle/warp_oracle.utils_warp against the reference's own lib/utils.py `warp` (frozen by oracle/make_golden.py)."""
+    g = golden_utils_warp
+    got = warp_oracle.utils_warp(torch.from_numpy(g[f"{name}.x"]), torch.from_numpy(g[f"{name}.flo"]))
+    assert np.array_equal(got.numpy(), g[f"{name}.out"])
+    if name == "uw_zero_12":      # align_corners=False: zero flow is NOT the identity (half-pixel shift towards the centre)
+        assert not np.allclose(got.numpy(), g[f"{name}.x"])

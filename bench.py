@@ -345,6 +345,8 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying one CUDA graph per step")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--l2-persist-mb", type=int, default=0,
+                    help="experiment: cudaLimitPersistingL2CacheSize in MB (the lookup's pyramid reads carry L2 evict_last hints)")
     ap.add_argument("--patients", type=int, default=150, help="cfg5 only")
     ap.add_argument("--slices", type=int, default=10, help="cfg5 only")
     args = ap.parse_args()
@@ -372,6 +374,13 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     _cabi.lib()  # fail loudly if the extension is missing
+    if args.l2_persist_mb:
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so.12")
+        torch.zeros(1, device=dev)
+        rc = rt.cudaDeviceSetLimit(6, ctypes.c_size_t(args.l2_persist_mb << 20))      # cudaLimitPersistingL2CacheSize
+        if rc:
+            sys.exit(f"cudaDeviceSetLimit(PersistingL2CacheSize, {args.l2_persist_mb} MB) failed: {rc}")
 
     P, C, H, W, IH, IW = wl["pairs"], wl["C"], wl["H"], wl["W"], wl["IH"], wl["IW"]
     K81 = LEVELS * (2 * RADIUS + 1) ** 2

@@ -62,6 +62,7 @@ struct LookupParams {
     int HW;
     int L;
     int lshift;     // log2(L) when L is a power of two, else -1
+    float l2_frac;  // fraction of pyramid lines fetched with L2 evict_last priority
     unsigned tiled; // bit l: level l is stored as 4x4 tiles (cardioflow.h: CF_LAYOUT_TILED4)
 };
 
@@ -81,9 +82,9 @@ __device__ __forceinline__ void classify(float c, int size, bool& nominal, bool&
 
 // The pyramid is re-read by every lookup of a CorrBlock (12x per frame pair) while each lookup streams its output
 // once: pyramid reads carry an L2 evict_last policy, output stores are streaming (st.global.cs).
-__device__ __forceinline__ uint64_t l2_evict_last_policy() {
+__device__ __forceinline__ uint64_t l2_evict_last_policy(float frac = 1.0f) {
     uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, %1;" : "=l"(pol) : "f"(frac));
     return pol;
 }
 // asynchronous global -> shared copies (LDGSTS): no staging registers, every copy of a warp is in flight at once;
@@ -113,13 +114,13 @@ __device__ __forceinline__ int win_base(int q) { return q * Geo<R>::QP + 4 * (q 
 // gx..gx+3) lives at ((y >> 2) * (wl / 4) + gx / 4) * 16 + (y & 3) * 4 words and the four rows of a tile share one DRAM atom.
 template <int R, int NW, bool VEC, bool TILED = false>
 __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __restrict__ img0, int hl, int wl, int w,
-                                              int lane, int ax, int ay, unsigned flags) {
+                                              int lane, int ax, int ay, unsigned flags, float l2_frac = 1.0f) {
     using G = Geo<R>;
     constexpr int PR = G::PR, PC = G::PC;
     constexpr int RPW = (PR + NW - 1) / NW;
     const int qq = lane >> 2, ch = lane & 3;
     const int img_words = hl * wl;
-    const uint64_t pol = l2_evict_last_policy();
+    const uint64_t pol = l2_evict_last_policy(l2_frac);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
         const int src = 4 * g + (qq & 3) + 16 * (qq >> 2);   // query served by this lane in group g
@@ -215,9 +216,9 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
         const unsigned flags = (dead ? kDead : 0u) | (nom_x ? kNomX : 0u) | (nom_y ? kNomY : 0u) | (lo_x ? kLoX : 0u) |
                                (lo_y ? kLoY : 0u);
         const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
-        if ((P.tiled >> l) & 1u) stage_windows<R, NW, true, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
-        else if (vec) stage_windows<R, NW, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
-        else stage_windows<R, NW, false>(win_s, img0, hl, wl, w, lane, ax, ay, flags);
+        if ((P.tiled >> l) & 1u) stage_windows<R, NW, true, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags, P.l2_frac);
+        else if (vec) stage_windows<R, NW, true>(win_s, img0, hl, wl, w, lane, ax, ay, flags, P.l2_frac);
+        else stage_windows<R, NW, false>(win_s, img0, hl, wl, w, lane, ax, ay, flags, P.l2_frac);
     }
 
     // taps: warp w computes taps w*JPW.. of both axes; x taps are shared, y taps stay in registers
@@ -350,9 +351,9 @@ __global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__
         const unsigned flags = (dead ? kDead : 0u) | (nom_x ? kNomX : 0u) | (nom_y ? kNomY : 0u) | (lo_x ? kLoX : 0u) |
                                (lo_y ? kLoY : 0u);
         const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
-        if ((P.tiled >> l) & 1u) stage_windows<R, 1, true, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
-        else if (vec) stage_windows<R, 1, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
-        else stage_windows<R, 1, false>(win_s, img0, hl, wl, 0, lane, ax, ay, flags);
+        if ((P.tiled >> l) & 1u) stage_windows<R, 1, true, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags, P.l2_frac);
+        else if (vec) stage_windows<R, 1, true>(win_s, img0, hl, wl, 0, lane, ax, ay, flags, P.l2_frac);
+        else stage_windows<R, 1, false>(win_s, img0, hl, wl, 0, lane, ax, ay, flags, P.l2_frac);
     }
     // x taps (registers) while the copies are in flight
     float xl[SIDE], xh[SIDE];
@@ -527,6 +528,8 @@ int launch_lookup(const float* pyramid, const LevelDims& d, const float* coords,
         if (((tiled_mask >> l) & 1u) && ((d.h[l] | d.w[l]) & 3))
             return fail(CF_ERR_BAD_ARG, "lookup: level %d (%dx%d) cannot be 4x4-tiled", l, d.h[l], d.w[l]);
     P.tiled = tiled_mask;
+    static const float frac = [] { const char* e = getenv("CF_L2_FRAC"); return e ? (float)atof(e) : 1.0f; }();   // tuning knob
+    P.l2_frac = frac;
     switch (r) {
         case 1: return launch_lookup_r<1>(P, s);
         case 2: return launch_lookup_r<2>(P, s);

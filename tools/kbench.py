@@ -29,6 +29,14 @@ if os.environ.get("KB_L2_FETCH"):
     v = ctypes.c_size_t()
     rt.cudaDeviceGetLimit(ctypes.byref(v), 5)
     print("L2 fetch granularity now", v.value)
+if os.environ.get("KB_L2_PERSIST_MB"):
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    torch.zeros(1, device=dev)
+    print("cudaDeviceSetLimit(PersistingL2CacheSize) ->", rt.cudaDeviceSetLimit(6, ctypes.c_size_t(int(os.environ["KB_L2_PERSIST_MB"]) << 20)))
+    v = ctypes.c_size_t()
+    rt.cudaDeviceGetLimit(ctypes.byref(v), 6)
+    print("persisting L2 set-aside now", v.value / 2**20, "MB; max", torch.cuda.get_device_properties(0).L2_cache_size / 2**20, "MB L2")
 lib = _cabi.lib()
 PEAK = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
 HBM, TF = PEAK["hbm_gbs"], PEAK["bf16_tflops"]

@@ -138,7 +138,7 @@ int cf_corr_build_layout(const float* f1, const float* f2, int B, int C, int H, 
         if (rc) return rc;
     }
     if (used_precision) *used_precision = used;
-    return launch_pool_chain(pyramid, d, (long)B * H * W, L, from_level, s);
+    return launch_pool_chain(pyramid, d, (long)B * H * W, L, from_level, s, tiled_mask ? *tiled_mask : 0u);
 }
 
 int cf_corr_pool(float* pyramid, int B, int H, int W, int L, int from_level, void* stream) {

@@ -95,7 +95,8 @@ int launch_sample_points(const float* locs, const float* src, int B, int C, int 
                          int mode, float* out, cudaStream_t s);
 
 int launch_pool2x2(const float* in, float* out, long n_img, int h, int w, cudaStream_t s);
-int launch_pool_chain(float* pyramid, const LevelDims& d, long n_img, int L, int from_level, cudaStream_t s);
+int launch_pool_chain(float* pyramid, const LevelDims& d, long n_img, int L, int from_level, cudaStream_t s,
+                      unsigned tiled_mask = 0 /* bit l: INPUT level l is stored as 4x4 tiles; outputs are row-major */);
 int launch_pool_chain_bwd(float* gpyr, const LevelDims& d, long n_img, int L, cudaStream_t s);
 
 int launch_corr_simt(const float* f1, const float* f2, int B, int C, int HW, float* level0, cudaStream_t s);

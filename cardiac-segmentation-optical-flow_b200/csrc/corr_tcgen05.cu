@@ -60,6 +60,7 @@ struct GemmParams {
     int ts_cta;
     float* dbg;          // bring-up only: raw accumulators + smem operand dump of CTA 0 (null in production)
     int tile_l0;         // W == 32 epilogue: write level 0 as 4x4 tiles (CF_LAYOUT_TILED4)
+    int tile_l1;         // generic epilogue: write the fused level 1 as 4x4 tiles
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -443,7 +444,12 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         o.y = pool4(top[2], top[3], bot[2], bot[3]);
                         o.z = pool4(top[4], top[5], bot[4], bot[5]);
                         o.w = pool4(top[6], top[7], bot[6], bot[7]);
-                        if (row_ok) *reinterpret_cast<float4*>(l1row + (size_t)(pair0 + j) * W2 + 4 * m) = o;
+                        if (row_ok) {
+                            const int y1 = pair0 + j;
+                            float* dst = P.tile_l1 ? l1row + ((size_t)((y1 >> 2) * (W2 >> 2) + m) * 16 + (y1 & 3) * 4)
+                                                   : l1row + (size_t)y1 * W2 + 4 * m;
+                            *reinterpret_cast<float4*>(dst) = o;
+                        }
                     }
                 }
             }
@@ -610,9 +616,22 @@ int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, i
     if (w32 && L > 2) P.level2 = levels[2];
     if (w32 && L > 3 && (H % 8) == 0 && (tiles_per % 2) == 0 && P.n_tiles % split == 0) P.level3 = levels[3];
     *levels_done = P.level3 ? 4 : (P.level2 ? 3 : (level1 ? 2 : 1));
-    // level 0 as 4x4 tiles (fewer DRAM atoms per lookup window): only the register-resident epilogue can reorder for free
-    P.tile_l0 = (w32 && allow_tiled && tiled_mask) ? 1 : 0;
-    if (P.tile_l0) *tiled_mask = 1u;
+    // Levels as 4x4 tiles (fewer DRAM atoms per lookup window; worth it for rows >= 128 B).  W == 32: the register-resident
+    // epilogue reorders level 0 for free.  Other widths: the fused level 1 is tiled by addressing (the pooling chain reads it
+    // with its tiled-input kernel); level 0 stays row-major there -- a 5-D tensor-map store of 16-byte tile rows (boxes
+    // {4,8,1,1,128} and {4 of 16,8,1,128,1}, SWIZZLE_128B) faulted on B200 in both forms and was dropped.
+    // Measured at cfg4: tiling level 1 speeds the lookup up by 7 % (183 -> 171 us) but a 128-column accumulator tile holds one
+    // level-1 row only, so a 64 B tile is completed by four different tiles' scattered 16 B stores and the build loses more
+    // (3.85 -> 4.13 ms per step): bit 1 is off by default.
+    const char* tile_env = getenv("CF_GEMM_TILED");                  // bit 0: level 0 (W == 32), bit 1: level 1 (other widths)
+    const int tile_knob = tile_env ? atoi(tile_env) : 1;
+    const bool can_tile = allow_tiled && tiled_mask != nullptr && g_dbg == nullptr;
+    if (w32) {
+        P.tile_l0 = (can_tile && (tile_knob & 1)) ? 1 : 0;
+    } else if (can_tile) {
+        P.tile_l1 = (level1 && (tile_knob & 2) && (W / 2) % 4 == 0 && (H / 2) % 4 == 0 && W / 2 >= 32) ? 1 : 0;
+    }
+    if (tiled_mask) *tiled_mask = (P.tile_l0 ? 1u : 0u) | (P.tile_l1 ? 2u : 0u);
 
     CUtensorMap tmA, tmB, tmC;
     int rc;

@@ -192,6 +192,26 @@ def test_full_size_properties_cfg4():
     assert np.abs(blk(coords)[:1].cpu().numpy() - want).max() <= 2e-5 * np.abs(want).max()
 
 
+@pytest.mark.parametrize("hw,c,want_mask", [((64, 64), 128, 2), ((32, 64), 64, 2), ((64, 32), 256, 1), ((40, 96), 32, 0), ((64, 128), 32, 0)])
+def test_tiled_levels_generic_epilogue(monkeypatch, hw, c, want_mask):
+    """Widths other than 32: the fused level 1 is tiled by addressing when its rows are >= 128 B and the pooling chain reads
+    the tiled level; pyramids and lookups must be bit-identical to the row-major build."""
+    h, w = hw
+    g = torch.Generator().manual_seed(h * w + c)
+    f1, f2 = torch.randn(2, c, h, w, generator=g).to(DEV), torch.randn(2, c, h, w, generator=g).to(DEV)
+    monkeypatch.setenv("CF_GEMM_TILED", "3")      # level-1 tiling is off by default (it costs the build more than the lookup gains)
+    monkeypatch.setenv("CARDIOFLOW_TILED", "0")
+    plain = cf.CorrBlock(f1, f2, precision="bf16")
+    monkeypatch.setenv("CARDIOFLOW_TILED", "1")
+    tiled = cf.CorrBlock(f1, f2, precision="bf16")
+    assert plain._tiled_mask == 0 and tiled._tiled_mask == want_mask
+    for a, b in zip(plain.corr_pyramid, tiled.corr_pyramid):
+        assert a.shape == b.shape and torch.equal(a, b)
+    for s in (0.0, 1.3, 50.0):
+        coords = cf.coords_grid(2, h, w, device=DEV) + s * torch.randn(2, 2, h, w, generator=g).to(DEV)
+        assert torch.equal(plain(coords), tiled(coords))
+
+
 def test_tiled_level0_is_invisible(monkeypatch):
     """The tensor-core builder stores level 0 as 4x4 tiles when no gradient is needed (cf_corr_build_layout /
     cf_corr_lookup_layout).  Nothing observable may change: pyramid values and every lookup are bit-identical to the

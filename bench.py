@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the optical-flow hot path: frame-pairs/sec for (correlation pyramid build + 12 lookups + warp).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg4|cfg5 [--patients P --slices S]] [--no-graph]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg3|cfg4|cfg5 [--patients P --slices S]] [--no-graph]
 
 One "step" = one (patient, slice) cine unit of BASELINE.json configs[1]: 29 consecutive frame pairs with
 256-channel 32x32 feature maps -> CorrBlock build (batched over the 29 pairs), 12 CorrBlock lookups, and the
@@ -35,6 +35,8 @@ WORKLOADS = {
     "cfg5": dict(pairs=29, C=256, H=32, W=32, IH=256, IW=256,
                  desc="configs[4]: cohort of patients x slices cine units (29 pairs each, 32x32 fmaps, 256^2 frames + 4-class masks), "
                       "sharded by (patient, slice), one NCCL gather"),
+    "cfg3": dict(items=300, pairs=300, C=1, H=28, W=28, IH=224, IW=224,
+                 desc="configs[2]: SpatialTransformer warp of image + one-hot 4-class masks by dense flow, 10 slices x 30 frames at 224^2"),
     "cfg4": dict(pairs=64, C=256, H=64, W=64, IH=512, IW=512,
                  desc="configs[3]: 64 frame pairs, 256-ch fmaps 64x64, materialised volume, 12 lookups, 64 warps"),
 }
@@ -159,6 +161,28 @@ def run_reference_arm(args, wl):
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     from oracle import corr_oracle, warp_oracle
+    if args.workload == "cfg3":          # the warp alone: 30 of the 300 five-channel frames per step
+        n, IH, IW = 30, wl["IH"], wl["IW"]
+        g = torch.Generator().manual_seed(1003)
+        src, flow = torch.rand(n, 5, IH, IW, generator=g), torch.randn(n, 2, IH, IW, generator=g) * 3
+        st = warp_oracle.SpatialTransformer((IH, IW))
+        with torch.no_grad():
+            for _ in range(args.warmup):
+                st(flow=flow, original=src)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                st(flow=flow, original=src)
+            dt = time.perf_counter() - t0
+        value = n * args.steps / dt
+        desc = f"{n} of {wl['items']} frames per step (5-channel SpatialTransformer warp), torch CPU fp32"
+        print(json.dumps({"impl": "reference", "metric": "frames warped/sec (image + 4 one-hot masks, 224^2)", "value": value,
+                          "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                          "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "f32", "data": "synthetic", "config": {"workload": "cfg3: " + wl["desc"], "sample": desc},
+                          "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port", "sample": desc},
+                          "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                          "gpu_launches": 0}), flush=True)
+        return
     unit = make_unit(dict(wl, pairs=sample), seed=1002)
     st = warp_oracle.SpatialTransformer((wl["IH"], wl["IW"]))
 
@@ -333,6 +357,111 @@ def run_cohort(args, wl):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------ cfg3 warp batch
+def run_warp_batch(args, wl):
+    """BASELINE.json configs[2]: SpatialTransformer warp of image + one-hot 4-class masks (5 channels) by a dense smooth
+    flow, 10 slices x 30 frames at 224^2 in one batch.  A step = one cf_warp2d launch over the 300 items."""
+    import cardioflow_b200 as cf
+    from cardioflow_b200 import _cabi
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        sys.exit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    _cabi.lib()
+    B, IH, IW, C = wl["items"], wl["IH"], wl["IW"], 5
+
+    def make(seed, pin=False):
+        g = torch.Generator().manual_seed(seed)
+        img = torch.rand(B, 1, IH, IW, generator=g)
+        yy, xx = torch.meshgrid(torch.arange(IH), torch.arange(IW), indexing="ij")
+        rad = ((yy - IH / 2) ** 2 + (xx - IW / 2) ** 2).float().sqrt() / (IH / 2)
+        label = (rad < 0.2).long() * 3 + ((rad >= 0.2) & (rad < 0.35)).long() * 2 + ((rad >= 0.35) & (rad < 0.6)).long()
+        onehot = torch.nn.functional.one_hot(label, 4).permute(2, 0, 1).float()[None].expand(B, 4, IH, IW)
+        src = torch.cat([img, onehot], 1).contiguous()
+        flow = torch.nn.functional.interpolate(torch.randn(B, 2, 7, 7, generator=g) * 4.0, size=(IH, IW), mode="bicubic",
+                                               align_corners=True).contiguous()
+        if pin:
+            return src.pin_memory(), flow.pin_memory()
+        return src.to(dev), flow.to(dev)
+
+    n_sets = 2       # 2 x (361 + 120) MB of inputs + 361 MB written per step: every step streams > 126 MB L2
+    sets = [make(1003 + 31 * rank + s) for s in range(n_sets)]
+    out = torch.empty(B, C, IH, IW, dtype=torch.float32, device=dev)
+    st = cf.SpatialTransformer((IH, IW)).to(dev)
+    with torch.no_grad():
+        for i in range(max(args.warmup, 3)):
+            cf.warp(sets[i % n_sets][0], sets[i % n_sets][1], out=out)
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            cf.warp(sets[i % n_sets][0], sets[i % n_sets][1], out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        clocks = sampler.stop()
+        if dist:
+            dist.barrier()
+        ms_total = e0.elapsed_time(e1)
+        # end to end: pinned host buffers -> module API -> pinned host result
+        h_src, h_flow = make(1003 + 31 * rank, pin=True)
+        h_out = torch.empty(B, C, IH, IW, dtype=torch.float32).pin_memory()
+        d_src, d_flow = torch.empty_like(sets[0][0]), torch.empty_like(sets[0][1])
+        e2e_steps = args.e2e_steps or min(args.steps, 10)
+
+        def e2e_step():
+            d_src.copy_(h_src, non_blocking=True)
+            d_flow.copy_(h_flow, non_blocking=True)
+            h_out.copy_(st(flow=d_flow, original=d_src), non_blocking=True)
+
+        e2e_step()
+        torch.cuda.synchronize()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        b_.record()
+        torch.cuda.synchronize()
+        e2e_ms = a.elapsed_time(b_)
+    if dist:
+        t = torch.tensor([ms_total, e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms = t.tolist()
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        peak = json.load(open(peaks_path))["hbm_gbs"] if os.path.exists(peaks_path) else 6650.0
+        nbytes = 4 * B * IH * IW * (2 * C + 2)
+        ms = ms_total / args.steps
+        line = {
+            "metric": "frames warped/sec (image + 4 one-hot masks, 224^2)", "value": world * B * args.steps / (ms_total * 1e-3),
+            "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "cfg3: " + wl["desc"], "items_per_step_per_gpu": B, "channels": C,
+                       "l2": f"inputs rotate over {n_sets} sets; a step reads 482 MB and writes 301 MB (> 126 MB L2)"},
+            "clocks": clocks,
+            "e2e": {"value": world * B * e2e_steps / (e2e_ms * 1e-3), "unit": "frames/s",
+                    "h2d_bytes_per_step": int(h_src.numel() * 4 + h_flow.numel() * 4), "d2h_bytes_per_step": int(h_out.numel() * 4),
+                    "steps": e2e_steps},
+            "gpu_launches": args.steps,
+            "roofline": {"kernel": "warp2d_tile_kernel", "bound": "hbm", "achieved": nbytes / (ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": nbytes / (ms * 1e-3) / 1e9 / peak, "traffic": None,
+                         "algorithmic_bytes_per_launch": nbytes, "avg_launch_ms": ms},
+        }
+        print(json.dumps(line), flush=True)
+    if dist:
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------------------ GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -357,6 +486,8 @@ def main():
         return run_reference_arm(args, wl)
     if args.workload == "cfg5":
         return run_cohort(args, wl)
+    if args.workload == "cfg3":
+        return run_warp_batch(args, wl)
 
     import cardioflow_b200 as cf
     from cardioflow_b200 import _cabi

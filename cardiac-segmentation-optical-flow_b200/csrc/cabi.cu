@@ -297,4 +297,14 @@ int cf_upsample_convex(const float* field, const float* mask, int B, int C, int 
     return launch_upsample_convex(field, mask, B, C, H, W, scale, out, (cudaStream_t)stream);
 }
 
+int cf_upsample_convex_bwd(const float* field, const float* mask, const float* grad_out, int B, int C, int H, int W, int factor,
+                           float scale, float* grad_field, float* grad_mask, void* stream) {
+    CF_REQUIRE(field && mask && grad_out, CF_ERR_BAD_ARG, "cf_upsample_convex_bwd: null pointer");
+    CF_REQUIRE(grad_field || grad_mask, CF_ERR_BAD_ARG, "cf_upsample_convex_bwd: neither grad_field nor grad_mask requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_upsample_convex_bwd: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    CF_REQUIRE(factor == 8, CF_ERR_UNSUPPORTED, "cf_upsample_convex_bwd: factor %d (the reference only has 8)", factor);
+    CF_REQUIRE(aligned16(grad_out), CF_ERR_BAD_ARG, "cf_upsample_convex_bwd: grad_out must be 16-byte aligned");
+    return launch_upsample_convex_bwd(field, mask, grad_out, B, C, H, W, scale, grad_field, grad_mask, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -161,6 +161,12 @@ CF_API int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H
 CF_API int cf_upsample_convex(const float* field, const float* mask, int B, int C, int H, int W, int factor, float scale,
                        float* out, void* stream);
 
+/* Backward of cf_upsample_convex (autograd of the same two reference methods): grad_out [B,C,8H,8W] ->
+ * grad_field [B,C,H,W] (accumulated with atomics: zero-initialised by the caller; may be NULL) and grad_mask [B,576,H,W]
+ * (written; may be NULL). */
+CF_API int cf_upsample_convex_bwd(const float* field, const float* mask, const float* grad_out, int B, int C, int H, int W,
+                           int factor, float scale, float* grad_field, float* grad_mask, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

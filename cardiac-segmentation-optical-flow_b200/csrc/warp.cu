@@ -126,8 +126,10 @@ __device__ __noinline__ void warp2d_general(const float* __restrict__ img, float
 
 constexpr int kTileW = 32, kTileH = 16;   // CTA tile: 8 warps, each 32 pixels x 2 rows (lane = column)
 
-template <bool FASTDIV>
-__global__ void __launch_bounds__(256, 4) warp2d_tile_kernel(const float* __restrict__ flow, const float* __restrict__ src,
+// UNROLL / MINB measured at cfg3 (300 x {1,5} x 224^2): (2,4) 77 / 210 us, (4,4) 102 / 255, (5,3) 96 / 241, (2,5) 73 / 206,
+// (1,6) 71 / 196: the kernel wants resident warps (40 registers, 6 CTAs per SM), not deeper unrolling.
+template <bool FASTDIV, int UNROLL = 1, int MINB = 6>
+__global__ void __launch_bounds__(256, MINB) warp2d_tile_kernel(const float* __restrict__ flow, const float* __restrict__ src,
                                                              float* __restrict__ out, int B, int C, int H, int W, float ry,
                                                              float rx) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(256, 4) warp2d_tile_kernel(const float* __rest
             const float w00b = __fmul_rn(al1, bl1), w01b = __fmul_rn(ah1, bl1), w10b = __fmul_rn(al1, bh1), w11b = __fmul_rn(ah1, bh1);
             const float* pa = img + (iy0 * W + ix0);
             const float* pb = img + (iy1 * W + ix1);
-#pragma unroll 2
+#pragma unroll UNROLL
             for (int c = 0; c < C; ++c, pa += HW, pb += HW, o += HW) {
                 const float a00 = __ldg(pa), a01 = __ldg(pa + 1), a10 = __ldg(pa + W), a11 = __ldg(pa + W + 1);
                 const float b00 = __ldg(pb), b01 = __ldg(pb + 1), b10 = __ldg(pb + W), b11 = __ldg(pb + W + 1);

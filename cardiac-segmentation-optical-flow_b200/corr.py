@@ -56,7 +56,7 @@ class _CorrBuild(torch.autograd.Function):
     """(fmap1, fmap2) -> packed pyramid.  a2 + a3 of SURVEY.md 8(a)."""
 
     @staticmethod
-    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None, allow_tiled=False):
+    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None, allow_tiled=False, info=None):
         B, C, H, W = fmap1.shape
         lib = _cabi.lib()
         f1, f2 = _cabi.f32c(fmap1), _cabi.f32c(fmap2)
@@ -77,11 +77,11 @@ class _CorrBuild(torch.autograd.Function):
                                                  ws.data_ptr() if ws is not None else None, ws_bytes,
                                                  _cabi.ctypes.byref(used), _cabi.ctypes.byref(tiled), _cabi.stream()),
                         "cf_corr_build_layout")
-        _CorrBuild.last_tiled_mask = tiled.value
+        if info is not None:          # per-call report (thread-safe, unlike a class attribute)
+            info["tiled_mask"], info["used_precision"] = tiled.value, used.value
         ctx.save_for_backward(f1, f2)
         ctx.meta = (B, C, H, W, num_levels)
         ctx.used_precision = used.value
-        _CorrBuild.last_used_precision = used.value
         return pyramid
 
     @staticmethod
@@ -96,7 +96,7 @@ class _CorrBuild(torch.autograd.Function):
             _cabi.check(lib.cf_corr_pool_bwd(g.data_ptr(), B, H, W, L, s), "cf_corr_pool_bwd")
             _cabi.check(lib.cf_corr_volume_bwd(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W,
                                                gf1.data_ptr(), gf2.data_ptr(), s), "cf_corr_volume_bwd")
-        return gf1, gf2, None, None, None, None
+        return gf1, gf2, None, None, None, None, None
 
 
 class _CorrLookup(torch.autograd.Function):
@@ -181,9 +181,10 @@ class CorrBlock:
         # autograd on, the pyramid stays row-major: the backward kernels and any user arithmetic on corr_pyramid expect it.
         needs_grad = torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)
         allow_tiled = not needs_grad and os.environ.get("CARDIOFLOW_TILED", "1") != "0"
-        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer, allow_tiled)
-        self.used_precision = {0: "bf16", 1: "fp32"}.get(getattr(_CorrBuild, "last_used_precision", -1), "?")
-        self._tiled_mask = getattr(_CorrBuild, "last_tiled_mask", 0) if allow_tiled else 0
+        info = {}
+        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer, allow_tiled, info)
+        self.used_precision = {0: "bf16", 1: "fp32"}.get(info.get("used_precision", -1), "?")
+        self._tiled_mask = info.get("tiled_mask", 0)
         self._views = None
 
     @property

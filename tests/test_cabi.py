@@ -86,3 +86,40 @@ def test_shim_modules_resolve_to_this_package():
         spec.loader.exec_module(mod)
         for n in names:
             assert getattr(mod, n) is getattr(cf, n)
+
+
+def test_header_is_plain_c_and_a_c_host_links(tmp_path):
+    """include/cardioflow.h must be usable from a C host (the drop-in boundary has no C++ or torch types): compile a C
+    program with gcc -std=c99 -pedantic against the header, link libcardioflow.so, and make calls that need no GPU."""
+    import os
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.dirname(_cabi.LIB_PATH)
+    _cabi.lib()                                     # fails loudly if the library has not been built
+    src = tmp_path / "host.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include <string.h>
+#include "cardioflow.h"
+int main(void) {
+    int h = 0, w = 0;
+    if (cf_version() < 100) return 1;
+    if (cf_pyramid_level_dims(32, 32, 2, &h, &w) != CF_OK || h != 8 || w != 8) return 2;
+    if (cf_corr_pyramid_bytes(29, 32, 32, 4) != (size_t)161546240) return 3;
+    if (cf_warp2d(NULL, NULL, 1, 1, 8, 8, CF_MODE_BILINEAR, NULL, NULL) != CF_ERR_BAD_ARG) return 4;
+    if (strstr(cf_last_error(), "null") == NULL) return 5;
+    if (cf_upsample_convex((const float*)256, (const float*)512, 1, 2, 8, 8, 4, 4.0f, (float*)1024, NULL) != CF_ERR_UNSUPPORTED) return 6;
+    printf("c host ok\n");
+    return 0;
+}
+''')
+    exe = tmp_path / "host"
+    cmd = ["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", os.path.join(root, "include"), str(src), "-o", str(exe),
+           "-L", lib_dir, "-lcardioflow", "-Wl,-rpath," + lib_dir]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0 and "c host ok" in r.stdout, (r.returncode, r.stdout, r.stderr)

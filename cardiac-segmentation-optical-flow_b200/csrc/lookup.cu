@@ -62,6 +62,7 @@ struct LookupParams {
     int HW;
     int L;
     int lshift;     // log2(L) when L is a power of two, else -1
+    unsigned hw_magic;  // ceil(2^32 / HW)
     float l2_frac;  // fraction of pyramid lines fetched with L2 evict_last priority
     unsigned tiled; // bit l: level l is stored as 4x4 tiles (cardioflow.h: CF_LAYOUT_TILED4)
 };
@@ -121,20 +122,30 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
     const int qq = lane >> 2, ch = lane & 3;
     const int img_words = hl * wl;
     const uint64_t pol = l2_evict_last_policy(l2_frac);
+    // Owner side, once per lane: which of the 4 chunks its query's taps can read (nominal = the 2r+2 columns from
+    // (lo ? 1 : 0), else all PR) and the one row only a flipped floor can reach, packed for the staging lanes:
+    // bit 0 dead, bits 1-4 chunk needed, bits 5-8 skipped window row (15 = none)
+    unsigned info;
+    {
+        const int osh = VEC ? (ax & 3) : 0;
+        const int c0 = (flags & kNomX) ? ((flags & kLoX) ? 1 : 0) : 0;
+        const int c1 = (flags & kNomX) ? c0 + 2 * R + 1 : PR - 1;
+        unsigned need = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if ((4 * c + 3 >= osh + c0) && (4 * c <= osh + c1) && (4 * c < PC)) need |= 1u << c;
+        const unsigned oskip = (flags & kNomY) ? ((flags & kLoY) ? 0u : (unsigned)(PR - 1)) : 15u;
+        info = ((flags & kDead) ? 1u : 0u) | (need << 1) | (oskip << 5);
+    }
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
         const int src = 4 * g + (qq & 3) + 16 * (qq >> 2);   // query served by this lane in group g
         const int q_ax = __shfl_sync(0xffffffffu, ax, src);
         const int q_ay = __shfl_sync(0xffffffffu, ay, src);
-        const unsigned q_fl = __shfl_sync(0xffffffffu, flags, src);
-        const int sh = VEC ? (q_ax & 3) : 0;
-        const int gx = q_ax - sh + 4 * ch;                             // first image column of the chunk
-        // window columns the taps can read: nominal = the 2r+2 columns from (lo ? 1 : 0), else all PR
-        const int c0 = (q_fl & kNomX) ? ((q_fl & kLoX) ? 1 : 0) : 0;
-        const int c1 = (q_fl & kNomX) ? c0 + 2 * R + 1 : PR - 1;
-        const bool ch_need = !(q_fl & kDead) && (4 * ch + 3 >= sh + c0) && (4 * ch <= sh + c1) && (4 * ch < PC);
-        // the one row only a flipped floor can reach
-        const int skip = (q_fl & kNomY) ? ((q_fl & kLoY) ? 0 : PR - 1) : -1;
+        const unsigned q_in = __shfl_sync(0xffffffffu, info, src);
+        const int gx = (VEC ? (q_ax & ~3) : q_ax) + 4 * ch;          // first image column of the chunk
+        const bool ch_need = !(q_in & 1u) && ((q_in >> (1 + ch)) & 1u);
+        const int skip = (int)((q_in >> 5) & 15u);
         const bool col_in = (unsigned)gx < (unsigned)wl;              // VEC: chunks are entirely in or out
         const char* gq = TILED ? reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)gx * 4))
                                : reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)(q_ay + w) * wl + gx));
@@ -187,7 +198,9 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     const bool vec = (wl & 3) == 0;
 
     // ---- per-lane query (every warp holds the same 32 queries); batch index from CTA-uniform arithmetic ----
-    unsigned b = n0 / (unsigned)P.HW;
+    // n0 / HW by a host-computed reciprocal: ceil(2^32 / HW) over-estimates by at most one for n0 < 2^31
+    unsigned b = __umulhi(n0, P.hw_magic);
+    if (b * (unsigned)P.HW > n0) --b;
     unsigned p = n0 - b * (unsigned)P.HW + lane;
     if (p >= (unsigned)P.HW) { p -= (unsigned)P.HW; ++b; }      // H*W >= 256 > 32: at most one wrap
     float cx = 0.0f, cy = 0.0f;
@@ -251,17 +264,20 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     constexpr int K = SIDE * SIDE;
     const unsigned HW = (unsigned)P.HW;
     const int j0 = w * JPW;
-    float* ok[JPW];                               // one store pointer per output row, advanced by SIDE channels per x tap
+    // one store pointer per output row, advanced by SIDE channels per x tap; kept as byte addresses with a byte stride so
+    // that a step is one 64-bit add (element indices cost an extra LEA pair per store)
+    char* ok[JPW];
 #pragma unroll
-    for (int k = 0; k < JPW; ++k) ok[k] = P.out + ((size_t)b * P.L * K + (size_t)l * K + j0 + k) * HW + p;
-    const size_t ostep = (size_t)SIDE * HW;
+    for (int k = 0; k < JPW; ++k)
+        ok[k] = reinterpret_cast<char*>(P.out + ((size_t)b * P.L * K + (size_t)l * K + j0 + k) * HW + p);
+    const size_t ostep = (size_t)SIDE * HW * sizeof(float);
     const float* sq = win + win_base<R>(lane);
     if (dead) {
 #pragma unroll
         for (int i = 0; i < SIDE; ++i)
 #pragma unroll
             for (int k = 0; k < JPW; ++k)
-                if (j0 + k < SIDE) { __stcs(ok[k], 0.0f); ok[k] += ostep; }
+                if (j0 + k < SIDE) { __stcs(reinterpret_cast<float*>(ok[k]), 0.0f); ok[k] += ostep; }
         return;
     }
     if (fast) {
@@ -282,7 +298,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                     acc = fmaf(r[k][i + 1], __fmul_rn(xh, ywl[k]), acc);
                     acc = fmaf(r[k + 1][i], __fmul_rn(xl, ywh[k]), acc);
                     acc = fmaf(r[k + 1][i + 1], __fmul_rn(xh, ywh[k]), acc);
-                    __stcs(ok[k], acc);
+                    __stcs(reinterpret_cast<float*>(ok[k]), acc);
                     ok[k] += ostep;
                 }
             }
@@ -300,7 +316,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                     acc = fmaf(t[1], __fmul_rn(xh, ywl[k]), acc);
                     acc = fmaf(t[PC], __fmul_rn(xl, ywh[k]), acc);
                     acc = fmaf(t[PC + 1], __fmul_rn(xh, ywh[k]), acc);
-                    __stcs(ok[k], acc);
+                    __stcs(reinterpret_cast<float*>(ok[k]), acc);
                     ok[k] += ostep;
                 }
             }
@@ -512,6 +528,7 @@ LookupParams make_params(const float* pyramid, const LevelDims& d, const float* 
     P.N = (long)B * H * W;
     P.HW = H * W;
     P.L = L;
+    P.hw_magic = (unsigned)(((1ull << 32) + (unsigned long long)(H * W) - 1) / (unsigned long long)(H * W));
     P.lshift = -1;
     for (int k = 0; k < 4; ++k)
         if ((1 << k) == L) P.lshift = k;

@@ -287,6 +287,14 @@ int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W
     return launch_warp2d_xy(flow, src, B, C, H, W, out, (cudaStream_t)stream);
 }
 
+int cf_warp2d_xy_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W, float* grad_src,
+                     float* grad_flow, void* stream) {
+    CF_REQUIRE(flow && src && grad_out, CF_ERR_BAD_ARG, "cf_warp2d_xy_bwd: null pointer");
+    CF_REQUIRE(grad_src || grad_flow, CF_ERR_BAD_ARG, "cf_warp2d_xy_bwd: neither grad_src nor grad_flow requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_warp2d_xy_bwd: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    return launch_warp2d_xy_bwd(flow, src, grad_out, B, C, H, W, grad_src, grad_flow, (cudaStream_t)stream);
+}
+
 int cf_upsample_convex(const float* field, const float* mask, int B, int C, int H, int W, int factor, float scale, float* out,
                        void* stream) {
     CF_REQUIRE(field && mask && out, CF_ERR_BAD_ARG, "cf_upsample_convex: null pointer");

@@ -117,6 +117,8 @@ int launch_lookup_taps(const LevelDims& d, const float* coords, int B, int H, in
 int launch_lookup_bwd(const LevelDims& d, const float* coords, const float* go, int B, int H, int W, int L,
                       int r, float* gpyr, cudaStream_t s);
 
+int launch_warp2d_xy_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W, float* gsrc,
+                         float* gflow, cudaStream_t s);
 int launch_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, cudaStream_t s);
 int launch_upsample_convex_bwd(const float* field, const float* mask, const float* gout, int B, int C, int H, int W, float scale,
                                float* gfield, float* gmask, cudaStream_t s);

@@ -15,8 +15,17 @@ namespace cf {
 namespace {
 
 // ---------------------------------------------------------------------------------------------- warp backward
+// lib/utils.warp coordinates (utils.py:49-50 + grid_sample align_corners=False): see warp2d_xy_kernel below
+__device__ __forceinline__ float utils_warp_coord_bwd(float p, float d1 /* max(S-1,1) */, float size) {
+    const float n = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, p), d1), 1.0f);
+    return __fmul_rn(__fsub_rn(__fmul_rn(__fadd_rn(n, 1.0f), size), 1.0f), 0.5f);
+}
+
 // One thread per output pixel, all C channels: d(out)/d(src) is scattered with atomics (several output pixels
 // may sample the same source texel), d(out)/d(flow) is a per-pixel reduction over channels (no atomics).
+// XY = false: SpatialTransformer (flow ch0 displaces rows, align_corners=True); XY = true: lib/utils.warp (flow ch0 displaces
+// columns, align_corners=False: d(u)/d(n) = S/2, d(n)/d(p) = 2/max(S-1,1)).
+template <bool XY>
 __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict__ flow, const float* __restrict__ src,
                                                          const float* __restrict__ go, float* __restrict__ gsrc,
                                                          float* __restrict__ gflow, int C, int H, int W, float ry, float rx,
@@ -29,8 +38,10 @@ __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict
     const long b = row / H;
     const size_t HW = (size_t)H * W, pix = (size_t)y * W + x;
     const float s1y = (float)(H - 1), s1x = (float)(W - 1);
-    const float uy = warp_coord(__fadd_rn((float)y, __ldg(flow + (b * 2 + 0) * HW + pix)), s1y, ry);
-    const float ux = warp_coord(__fadd_rn((float)x, __ldg(flow + (b * 2 + 1) * HW + pix)), s1x, rx);
+    const float fl0 = __ldg(flow + (b * 2 + 0) * HW + pix), fl1 = __ldg(flow + (b * 2 + 1) * HW + pix);
+    const float d1y = (float)max(H - 1, 1), d1x = (float)max(W - 1, 1);
+    const float uy = XY ? utils_warp_coord_bwd(__fadd_rn((float)y, fl1), d1y, (float)H) : warp_coord(__fadd_rn((float)y, fl0), s1y, ry);
+    const float ux = XY ? utils_warp_coord_bwd(__fadd_rn((float)x, fl0), d1x, (float)W) : warp_coord(__fadd_rn((float)x, fl1), s1x, rx);
     const Tap tp = make_tap(uy, ux);
     const float fx = floorf(ux), fy = floorf(uy);
     // ATen names: (ix_nw, iy_nw) = (fx, fy); se = nw + 1
@@ -65,11 +76,19 @@ __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict
         }
     }
     if (gflow) {
-        // grid_sampler un-normalise: d(u)/d(n) = (S-1)/2 ; reference normalise: d(n)/d(p) = 2/(S-1)
-        const float gx = __fdiv_rn(__fmul_rn(__fmul_rn(gix, __fmul_rn(s1x, 0.5f)), 2.0f), s1x);
-        const float gy = __fdiv_rn(__fmul_rn(__fmul_rn(giy, __fmul_rn(s1y, 0.5f)), 2.0f), s1y);
-        gflow[(b * 2 + 0) * HW + pix] = gy;   // flow channel 0 displaces rows
-        gflow[(b * 2 + 1) * HW + pix] = gx;
+        if (XY) {
+            // grid_sampler un-normalise (align_corners=False): d(u)/d(n) = S/2 ; utils.warp normalise: d(n)/d(p) = 2/max(S-1,1)
+            const float gx = __fdiv_rn(__fmul_rn(__fmul_rn(gix, __fmul_rn((float)W, 0.5f)), 2.0f), d1x);
+            const float gy = __fdiv_rn(__fmul_rn(__fmul_rn(giy, __fmul_rn((float)H, 0.5f)), 2.0f), d1y);
+            gflow[(b * 2 + 0) * HW + pix] = gx;   // flow channel 0 displaces columns
+            gflow[(b * 2 + 1) * HW + pix] = gy;
+        } else {
+            // grid_sampler un-normalise: d(u)/d(n) = (S-1)/2 ; reference normalise: d(n)/d(p) = 2/(S-1)
+            const float gx = __fdiv_rn(__fmul_rn(__fmul_rn(gix, __fmul_rn(s1x, 0.5f)), 2.0f), s1x);
+            const float gy = __fdiv_rn(__fmul_rn(__fmul_rn(giy, __fmul_rn(s1y, 0.5f)), 2.0f), s1y);
+            gflow[(b * 2 + 0) * HW + pix] = gy;   // flow channel 0 displaces rows
+            gflow[(b * 2 + 1) * HW + pix] = gx;
+        }
     }
 }
 
@@ -154,8 +173,16 @@ __global__ void __launch_bounds__(128) sample_points_kernel(const float* __restr
 int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W, float* gsrc,
                       float* gflow, cudaStream_t s) {
     const long total = (long)B * H * W;
-    warp2d_bwd_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, src, go, gsrc, gflow, C, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
+    warp2d_bwd_kernel<false><<<cdiv(total, 256), 256, 0, s>>>(flow, src, go, gsrc, gflow, C, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
     CF_CHECK_LAUNCH("warp2d_bwd_kernel");
+    return CF_OK;
+}
+
+int launch_warp2d_xy_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W, float* gsrc,
+                         float* gflow, cudaStream_t s) {
+    const long total = (long)B * H * W;
+    warp2d_bwd_kernel<true><<<cdiv(total, 256), 256, 0, s>>>(flow, src, go, gsrc, gflow, C, H, W, 0.0f, 0.0f, total);
+    CF_CHECK_LAUNCH("warp2d_bwd_kernel<xy>");
     return CF_OK;
 }
 

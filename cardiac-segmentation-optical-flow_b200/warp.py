@@ -79,21 +79,40 @@ def warp_onehot_argmax(flow, label, num_classes=4):
     return out
 
 
+class _UtilsWarp(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, flo):
+        f, src = _cabi.f32c(flo), _cabi.f32c(x)
+        B, C, H, W = src.shape
+        out = torch.empty_like(src)
+        with torch.cuda.device(src.device):
+            _cabi.check(_cabi.lib().cf_warp2d_xy(f.data_ptr(), src.data_ptr(), B, C, H, W, out.data_ptr(), _cabi.stream()),
+                        "cf_warp2d_xy")
+        ctx.save_for_backward(f, src)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        f, src = ctx.saved_tensors
+        B, C, H, W = src.shape
+        go = grad_out.contiguous().float()
+        need_src, need_flow = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gsrc = torch.zeros_like(src) if need_src else None
+        gflow = torch.empty_like(f) if need_flow else None
+        with torch.cuda.device(src.device):
+            _cabi.check(_cabi.lib().cf_warp2d_xy_bwd(f.data_ptr(), src.data_ptr(), go.data_ptr(), B, C, H, W,
+                                                     gsrc.data_ptr() if need_src else None,
+                                                     gflow.data_ptr() if need_flow else None, _cabi.stream()),
+                        "cf_warp2d_xy_bwd")
+        return gsrc, gflow
+
+
 def utils_warp(x, flo):
     """Drop-in for ``nnunet.lib.utils.warp(x, flo)`` (/root/reference/nnunet/lib/utils.py:29-59, called at
-    SegFlowGaussian.py:1044): x [B,C,H,W], flo [B,2,H,W] with channel 0 = x displacement; grid_sample defaults
-    (bilinear, zeros, align_corners=False).  Forward only."""
+    SegFlowGaussian.py:1044 inside the training graph): x [B,C,H,W], flo [B,2,H,W] with channel 0 = x displacement;
+    grid_sample defaults (bilinear, zeros, align_corners=False).  Differentiable w.r.t. both arguments."""
     _check_pair(flo, x)
-    _cabi.require_cuda(x, flo)
-    if torch.is_grad_enabled() and (x.requires_grad or flo.requires_grad):
-        raise NotImplementedError("utils_warp: the CUDA path is forward-only; call it under torch.no_grad()")
-    f, src = _cabi.f32c(flo), _cabi.f32c(x)
-    B, C, H, W = src.shape
-    out = torch.empty_like(src)
-    with torch.cuda.device(src.device):
-        _cabi.check(_cabi.lib().cf_warp2d_xy(f.data_ptr(), src.data_ptr(), B, C, H, W, out.data_ptr(), _cabi.stream()),
-                    "cf_warp2d_xy")
-    return out
+    return _UtilsWarp.apply(x, flo)
 
 
 def warp_taps(flow):

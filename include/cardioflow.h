@@ -154,6 +154,12 @@ CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, i
  * bilinear, zero padding, align_corners=False.  src / out [B,C,H,W]. */
 CF_API int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, void* stream);
 
+/* Backward of cf_warp2d_xy (the reference warps the looked-up correlation features inside the training graph,
+ * SegFlowGaussian.py:1044): grad_src accumulates with atomics (zero-initialised by the caller; may be NULL), grad_flow is
+ * written (may be NULL). */
+CF_API int cf_warp2d_xy_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W,
+                     float* grad_src, float* grad_flow, void* stream);
+
 /* Convex 8x upsampling (8(f) row 3): replaces `upsample_flow` (SegFlowGaussian.py:846-857, C = 2) and `upsample_seg`
  * (:860-871, C = 4): out[n,c,8y+i,8x+j] = sum_k softmax_k(mask[n,k*64+i*8+j,y,x]) * scale * field[n,c,y+ky-1,x+kx-1],
  * k = ky*3+kx, zeros outside.  field [B,C,H,W], mask [B,576,H,W], out [B,C,8H,8W]; the reference passes scale = 8

@@ -133,3 +133,20 @@ def test_utils_warp_full_size_against_oracle():
     assert rel_err(got.cpu().numpy(), warp_oracle.utils_warp(x, flo).numpy()) <= 1e-5
     with pytest.raises(RuntimeError):
         cf.utils_warp(x, flo)          # CPU tensors: no fallback
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 24, 24), (1, 5, 17, 40), (1, 2, 16, 16)])
+def test_utils_warp_backward_matches_autograd_of_the_oracle(shape):
+    """Gradients of cf_warp2d_xy w.r.t. x and flo against torch autograd through the CPU restatement of utils.py:29-59."""
+    import cardioflow_b200 as cf
+    from oracle import warp_oracle
+    b, c, h, w = shape
+    gen = torch.Generator().manual_seed(sum(shape))
+    x, flo = torch.rand(b, c, h, w, generator=gen), torch.randn(b, 2, h, w, generator=gen) * 2 + 0.3
+    gout = torch.randn(b, c, h, w, generator=gen)
+    xr, fr = x.clone().requires_grad_(), flo.clone().requires_grad_()
+    warp_oracle.utils_warp(xr, fr).backward(gout)
+    xg, fg = x.cuda().requires_grad_(), flo.cuda().requires_grad_()
+    cf.utils_warp(xg, fg).backward(gout.cuda())
+    assert rel_err(xg.grad.cpu().numpy(), xr.grad.numpy()) <= 1e-5
+    assert rel_err(fg.grad.cpu().numpy(), fr.grad.numpy()) <= 1e-4

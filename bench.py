@@ -26,7 +26,18 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner, warnings), so fd 1 is pointed
+# at stderr for the whole run and the result line goes to a duplicate of the original stdout.
+_RESULT_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
 import torch  # noqa: E402
+
+
+def emit(line):
+    _RESULT_OUT.write(json.dumps(line) + "\n")
+    _RESULT_OUT.flush()
+
 
 WORKLOADS = {
     # name: pairs, C, fmap H, W, image H, W
@@ -175,13 +186,13 @@ def run_reference_arm(args, wl):
             dt = time.perf_counter() - t0
         value = n * args.steps / dt
         desc = f"{n} of {wl['items']} frames per step (5-channel SpatialTransformer warp), torch CPU fp32"
-        print(json.dumps({"impl": "reference", "metric": "frames warped/sec (image + 4 one-hot masks, 224^2)", "value": value,
+        emit({"impl": "reference", "metric": "frames warped/sec (image + 4 one-hot masks, 224^2)", "value": value,
                           "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                           "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                           "dtype": "f32", "data": "synthetic", "config": {"workload": "cfg3: " + wl["desc"], "sample": desc},
                           "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port", "sample": desc},
                           "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                          "gpu_launches": 0}), flush=True)
+                          "gpu_launches": 0})
         return
     unit = make_unit(dict(wl, pairs=sample), seed=1002)
     st = warp_oracle.SpatialTransformer((wl["IH"], wl["IW"]))
@@ -211,7 +222,7 @@ def run_reference_arm(args, wl):
         "e2e": {"value": value, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------ cfg5 cohort
@@ -352,7 +363,7 @@ def run_cohort(args, wl):
         }
         if not all(check):
             line["error"] = "gathered rows differ from a local recomputation"
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist:
         dist.destroy_process_group()
 
@@ -457,7 +468,7 @@ def run_warp_batch(args, wl):
                          "unit": "GB/s", "frac": nbytes / (ms * 1e-3) / 1e9 / peak, "traffic": None,
                          "algorithmic_bytes_per_launch": nbytes, "avg_launch_ms": ms},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist:
         dist.destroy_process_group()
 
@@ -708,7 +719,7 @@ def main():
                                 "sample": f"{sample} of {P} pairs (per-pair CorrBlock + 12 lookups + warp), "
                                           f"torch CPU fp32 oracle, best of {reps}"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist:
         dist.destroy_process_group()
 

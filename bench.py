@@ -277,12 +277,24 @@ def run_cohort(args, wl):
     warped = torch.empty(P, 1, IH, IW, dtype=torch.float32, device=dev)
     WIDTH = 6   # row: [checksum of the last lookup, sum of the warped frames, 4 warped-label pixel counts]
 
-    def compute(u, row):
-        blk = cf.CorrBlock(u["f1"], u["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision, pyramid_buffer=pyramid)
+    # the pairs of a unit are independent: n parallel chains over contiguous sub-batches (cardioflow_b200.Lanes)
+    bounds = cf.lane_bounds(P, max(1, args.lanes))
+    lanes = cf.Lanes(len(bounds), dev)
+    lane_pyr = ([torch.empty(lib.cf_corr_pyramid_bytes(b - a, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
+                 for a, b in bounds] if len(bounds) > 1 else [pyramid])
+    lab = torch.empty(P, 1, IH, IW, dtype=torch.int64, device=dev)
+
+    def chain(u, j, a, b):
+        blk = cf.CorrBlock(u["f1"][a:b], u["f2"][a:b], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                           pyramid_buffer=lane_pyr[j])
         for k in range(ITERS):
-            blk(u["coords"][k], out=outs[k])
-        cf.warp(u["img"], u["flow"], out=warped)
-        lab = cf.warp_onehot_argmax(u["flow"], u["label"], num_classes=4)
+            blk(u["coords"][k, a:b], out=outs[k, a:b])
+        cf.warp(u["img"][a:b], u["flow"][a:b], out=warped[a:b])
+        lab[a:b].copy_(cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4))
+        return blk
+
+    def compute(u, row):
+        lanes.run(P, lambda j, a, b: chain(u, j, a, b))
         row[0] = outs[ITERS - 1].sum(dtype=torch.float64)
         row[1] = warped.sum(dtype=torch.float64)
         for c in range(4):
@@ -353,13 +365,13 @@ def run_cohort(args, wl):
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16 GEMM (fp32 accumulate) / f32 lookup+warp", "data": "synthetic",
             "config": {"workload": "cfg5: " + wl["desc"], "patients": args.patients, "slices": args.slices,
-                       "units": len(units), "units_on_rank0": len(mine), "pairs_per_unit": P,
+                       "units": len(units), "units_on_rank0": len(mine), "pairs_per_unit": P, "lanes": len(bounds),
                        "launch": "eager launches from Python, one unit at a time" if args.no_graph else "one CUDA graph replay per unit (build + 12 lookups + warp + mask warp + result row)",
                        "l2": "every unit has fresh inputs and writes 623 MB (> 126 MB L2)"},
             "clocks": clocks, "compute_ms_max_rank": compute_ms, "gather_ms_max_rank": gather_ms,
             "gather": {"collective": "all_gather_into_tensor (NCCL)" if world > 1 else "none (1 rank)",
                        "bytes_per_rank": int(rows[:len(mine)].numel() * 8), "rows_verified_on_rank0": check},
-            "gpu_launches": len(mine) * (2 + ITERS + 2),
+            "gpu_launches": len(mine) * (2 + ITERS + 2) * len(bounds),
         }
         if not all(check):
             line["error"] = "gathered rows differ from a local recomputation"
@@ -487,6 +499,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--l2-persist-mb", type=int, default=0,
                     help="experiment: cudaLimitPersistingL2CacheSize in MB (the lookup's pyramid reads carry L2 evict_last hints)")
+    ap.add_argument("--lanes", type=int, default=2,
+                    help="independent sub-batches of the step's pairs run as parallel stream branches (cardioflow_b200.Lanes); "
+                         "1 = one chain over the whole batch")
     ap.add_argument("--patients", type=int, default=150, help="cfg5 only")
     ap.add_argument("--slices", type=int, default=10, help="cfg5 only")
     args = ap.parse_args()
@@ -553,31 +568,63 @@ def main():
         for k in range(ITERS):
             blk(u["coords"][k], out=outs[k])
 
+    # Lanes: the pairs of a step are independent, so the step may run as n parallel chains (build -> 12 lookups -> warp
+    # each) over contiguous sub-batches; same kernels, same results, ramps and drains of one chain filled by the other.
+    bounds = cf.lane_bounds(P, max(1, args.lanes))
+    n_lanes = len(bounds)
+    lanes = cf.Lanes(n_lanes, dev)
+    lane_pyr = ([torch.empty(lib.cf_corr_pyramid_bytes(b - a, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
+                 for a, b in bounds] if n_lanes > 1 else [pyramid])
+
+    def lane_chain(u, j, a, b):
+        bk = cf.CorrBlock(u["f1"][a:b], u["f2"][a:b], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                          pyramid_buffer=lane_pyr[j])
+        for k in range(ITERS):
+            bk(u["coords"][k, a:b], out=outs[k, a:b])
+        cf.warp(u["img"][a:b], u["flow"][a:b], out=warped[a:b])
+        return bk
+
+    def step_lanes(u):
+        return lanes.run(P, lambda j, a, b: lane_chain(u, j, a, b))
+
     with torch.no_grad():
         blk = step(sets[0])
         used_precision = blk.used_precision
         torch.cuda.synchronize()
         use_graph = not args.no_graph
-        graphs = lookup_graphs = None
+        graphs = lookup_graphs = full_graphs = None
+        if n_lanes > 1:
+            step_lanes(sets[0])
+            torch.cuda.synchronize()
         if use_graph:
             # the step is launch-bound from Python (15 launches of 5-60 us): replay it as ONE CUDA graph per input set
-            graphs, lookup_graphs, blks = [], [], []
+            graphs, lookup_graphs, full_graphs, blks, keep = [], [], [], [], []
             for u in sets:
                 gph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(gph):
                     blks.append(step(u))
-                graphs.append(gph)
+                full_graphs.append(gph)
+            if n_lanes > 1:
+                for u in sets:
+                    gph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gph):
+                        keep.append(step_lanes(u))
+                    graphs.append(gph)
+            else:
+                graphs = full_graphs
             for u, bk in zip(sets, blks):          # the 12 lookups alone, for the roofline of the dominant kernel
                 gph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(gph):
                     lookups_only(u, bk)
                 lookup_graphs.append(gph)
 
-        def run_step(i, ev=None):
+        def run_step(i):
             if graphs:
                 graphs[i % n_sets].replay()
+            elif n_lanes > 1:
+                step_lanes(sets[i % n_sets])
             else:
-                step(sets[i % n_sets], ev)
+                step(sets[i % n_sets])
 
         for i in range(args.warmup):
             run_step(i)
@@ -590,25 +637,27 @@ def main():
         torch.cuda.synchronize()
         t_begin.record()
         for i in range(args.steps):
-            run_step(i, None if graphs else (ev_l0[i], ev_l1[i]))
+            run_step(i)
         t_end.record()
         torch.cuda.synchronize()
         clocks = sampler.stop()
         if dist:
             dist.barrier()
         ms_total = t_begin.elapsed_time(t_end)
-        if graphs:
-            # graph replays carry no inner events: time the 12-lookup graph right after a full step of the same set
-            # (same cache state as inside the step), CUDA events on the launching stream
-            n_ev = min(args.steps, 30)
-            for i in range(n_ev):
-                graphs[i % n_sets].replay()
+        # Roofline of the dominant kernel: the lookup launched over the WHOLE batch, alone on its stream (lane branches
+        # overlap, so per-kernel durations inside a lane step are not separable).  Graph replays carry no inner events:
+        # time the 12-lookup graph right after a full single-chain step of the same set (same cache state as inside a
+        # step); eager: events around the 12 lookups of a single-chain step.  CUDA events on the launching stream.
+        n_ev = min(args.steps, 30)
+        for i in range(n_ev):
+            if full_graphs:
+                full_graphs[i % n_sets].replay()
                 ev_l0[i].record()
                 lookup_graphs[i % n_sets].replay()
                 ev_l1[i].record()
-            torch.cuda.synchronize()
-        else:
-            n_ev = args.steps
+            else:
+                step(sets[i % n_sets], (ev_l0[i], ev_l1[i]))
+        torch.cuda.synchronize()
         lookup_ms = sorted(ev_l0[i].elapsed_time(ev_l1[i]) for i in range(n_ev))[n_ev // 2] / ITERS
 
         # ---- end-to-end leg: pinned host buffers -> public module API -> pinned host results ----
@@ -690,8 +739,13 @@ def main():
     if os.path.exists(tpath):
         with open(tpath) as f:
             traffic = json.load(f).get(args.workload)
-    n_pool = LEVELS - 1 if used_precision == "fp32" else LEVELS - 2
-    launches_per_step = 1 + n_pool + ITERS + 1
+    # fp32: SIMT GEMM + a pool launch per coarser level; bf16: transpose pre-pass + tcgen05 GEMM whose epilogue writes
+    # levels 0-1 (all four levels when the fmap width is 32) + a pool launch per remaining level; 12 lookups; 1 warp
+    if used_precision == "fp32":
+        build_launches = 1 + (LEVELS - 1)
+    else:
+        build_launches = 2 + (0 if (W == 32 and LEVELS <= 4) else LEVELS - 2)
+    launches_per_step = (build_launches + ITERS + 1) * n_lanes
 
     line = {
         "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
@@ -700,7 +754,9 @@ def main():
         "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step_per_gpu": P,
                    "corr_precision": used_precision, "cuda_graph": bool(graphs),
-                   "launch": "one CUDA graph replay per step" if graphs else "eager launches from Python",
+                   "lanes": n_lanes, "lane_pairs": [b - a for a, b in bounds],
+                   "launch": ("one CUDA graph replay per step" if graphs else "eager launches from Python")
+                             + (f", {n_lanes} parallel stream branches over contiguous sub-batches of the pairs" if n_lanes > 1 else ""),
                    "l2": f"inputs rotate over {n_sets} sets and each step writes "
                          f"{(pyr_floats * 4 + outs.numel() * 4) / 1e6:.0f} MB (> 126 MB L2)"},
         "clocks": clocks,
@@ -710,6 +766,7 @@ def main():
         "roofline": {"kernel": "lookup_kernel<4>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": lookup_bytes, "avg_launch_ms": lookup_ms,
+                     "launch_timed": f"all {P} pairs in one launch, alone on its stream",
                      "frac_of_nominal_8000": achieved / 8000.0},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

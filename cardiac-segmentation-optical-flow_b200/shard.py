@@ -48,3 +48,54 @@ def gather_results(local, n_units_total, rank=None, world_size=None, group=None)
     # rank r, slot j  ->  global unit j * world_size + r
     out = recv.view(world_size, per_rank, *local.shape[1:]).transpose(0, 1).reshape(per_rank * world_size, *local.shape[1:])
     return out[:n_units_total].contiguous()
+
+
+# ---------------------------------------------------------------------------------------------------------- lanes
+# Inside one GPU the same independence is worth ~14 % (tools/lanes.py, profiles/r1_lanes_experiment.log): a cine unit of
+# 29 pairs fills the 148 SMs for only ~3 waves per lookup, so every launch pays a latency ramp (coords -> windows -> first
+# stores) and a drain during which HBM idles.  Two sub-batches of the pairs, each a serial chain build -> 12 lookups -> warp on
+# its own stream, fill each other's ramps and drains.  Nothing is reordered inside a pair and results are bit-identical
+# (every kernel of the path treats batch items independently).
+
+def lane_bounds(n_items, n_lanes):
+    """Contiguous, near-equal split of ``n_items`` batch items over ``n_lanes`` lanes: [(begin, end), ...]; lanes that
+    would be empty are dropped."""
+    if n_items < 0 or n_lanes < 1:
+        raise ValueError(f"lane_bounds({n_items}, {n_lanes})")
+    cuts = [(n_items * j) // n_lanes for j in range(n_lanes + 1)]
+    return [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
+
+
+class Lanes:
+    """Run independent sub-batches on parallel CUDA streams, fork/joined on the current stream.
+
+        lanes = Lanes(2, device)
+        lanes.run(n_pairs, lambda j, a, b: chain(f1[a:b], f2[a:b], ...))      # returns the per-lane results
+
+    The fork and the join are event dependencies (``wait_stream``), so ``run`` is stream-ordered like a single kernel
+    launch and can be captured into one CUDA graph (the graph gets parallel branches).  With one lane ``fn`` runs inline
+    on the current stream.
+    """
+
+    def __init__(self, n_lanes, device=None):
+        if n_lanes < 1:
+            raise ValueError("n_lanes must be >= 1")
+        if not torch.cuda.is_available():
+            raise RuntimeError("Lanes needs a CUDA device: the path has no CPU fallback")
+        self.n_lanes = int(n_lanes)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(self.n_lanes)] if self.n_lanes > 1 else []
+
+    def run(self, n_items, fn):
+        bounds = lane_bounds(n_items, self.n_lanes)
+        if len(bounds) <= 1 or not self.streams:
+            return [fn(j, a, b) for j, (a, b) in enumerate(bounds)]
+        cur = torch.cuda.current_stream(self.device)
+        results = []
+        for (j, (a, b)), s in zip(enumerate(bounds), self.streams):
+            s.wait_stream(cur)
+            with torch.cuda.stream(s):
+                results.append(fn(j, a, b))
+        for s in self.streams[: len(bounds)]:
+            cur.wait_stream(s)
+        return results

@@ -238,3 +238,44 @@ def test_tiled_level0_is_invisible(monkeypatch):
     assert blk._tiled_mask == 0
     blk(coords[1]).mean().backward()
     assert fa.grad is not None and torch.isfinite(fa.grad).all()
+
+
+@pytest.mark.parametrize("n_lanes,graph", [(2, False), (3, False), (2, True)])
+def test_lanes_are_bit_identical_to_one_chain(n_lanes, graph):
+    """Sub-batches of the pairs on parallel streams (cardioflow_b200.Lanes) give the bytes of the single full-batch chain:
+    every kernel of the path treats batch items independently."""
+    g = torch.Generator().manual_seed(77)
+    P, C, H, W, IH = 7, 128, 32, 32, 96
+    f1, f2 = (torch.randn(P, C, H, W, generator=g).to(DEV) for _ in range(2))
+    coords = [(corr_oracle.coords_grid(P, H, W) + torch.randn(P, 2, H, W, generator=g) * 2.0).to(DEV) for _ in range(3)]
+    img, flow = torch.rand(P, 1, IH, IH, generator=g).to(DEV), (torch.randn(P, 2, IH, IH, generator=g) * 3).to(DEV)
+
+    def chain(a, b, outs, warped):
+        blk = cf.CorrBlock(f1[a:b], f2[a:b], radius=4)
+        for k, c in enumerate(coords):
+            blk(c[a:b], out=outs[k, a:b])
+        cf.warp(img[a:b], flow[a:b], out=warped[a:b])
+        return blk
+
+    def buffers():
+        return torch.full((3, P, 324, H, W), float("nan"), device=DEV), torch.full((P, 1, IH, IH), float("nan"), device=DEV)
+
+    with torch.no_grad():
+        ref_o, ref_w = buffers()
+        chain(0, P, ref_o, ref_w)
+        out_o, out_w = buffers()
+        lanes = cf.Lanes(n_lanes, DEV)
+        torch.cuda.synchronize()
+        if graph:
+            lanes.run(P, lambda j, a, b: chain(a, b, out_o, out_w))      # warm-up outside capture
+            torch.cuda.synchronize()
+            out_o.fill_(float("nan"))
+            gph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gph):
+                keep = lanes.run(P, lambda j, a, b: chain(a, b, out_o, out_w))
+            gph.replay()
+        else:
+            keep = lanes.run(P, lambda j, a, b: chain(a, b, out_o, out_w))
+        torch.cuda.synchronize()
+    assert len(keep) == n_lanes
+    assert torch.equal(out_o, ref_o) and torch.equal(out_w, ref_w)

@@ -79,3 +79,27 @@ def test_single_process_gather_is_identity():
     from cardioflow_b200.shard import gather_results
     x = torch.arange(12.0).view(4, 3)
     assert torch.equal(gather_results(x, 4, rank=0, world_size=1), x)
+
+
+def test_lane_bounds_partition():
+    from cardioflow_b200 import lane_bounds
+    assert lane_bounds(29, 2) == [(0, 14), (14, 29)]
+    assert lane_bounds(29, 1) == [(0, 29)]
+    assert lane_bounds(3, 4) == [(0, 1), (1, 2), (2, 3)]          # empty lanes are dropped
+    assert lane_bounds(0, 2) == []
+    for n in (1, 7, 29, 64, 300):
+        for k in (1, 2, 3, 4, 8):
+            b = lane_bounds(n, k)
+            assert b[0][0] == 0 and b[-1][1] == n and all(x[1] == y[0] for x, y in zip(b, b[1:]))
+            sizes = [e - a for a, e in b]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        lane_bounds(4, 0)
+
+
+def test_lanes_refuse_to_run_without_a_gpu():
+    from cardioflow_b200 import Lanes
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    with pytest.raises(RuntimeError):
+        Lanes(2)

@@ -162,10 +162,9 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
                 const uint32_t d = sq + (uint32_t)(NW * k * PC) * 4u;
                 if (VEC) {
                     const bool in = row_in && col_in;
-                    // src-size 0 writes 16 zero bytes and uses none of the source, but the request still goes to L2 (ncu: ~25 of
-                    // the ~89 sectors a query reads were zero-fill requests at scattered out-of-image addresses): point them
-                    // all at one valid address so that they collapse into a single sector per instruction
-                    cp_async_16(d, in ? gp : reinterpret_cast<const char*>(img0), in ? 16u : 0u, pol);
+                    // src-size 0: 16 zero bytes are written and nothing is read.  (A/B-tested under ncu: redirecting these requests to one
+                    // valid address changes neither the L2 sector counts nor the time -- profiles/r1_zfill_ab.log.)
+                    cp_async_16(d, gp, in ? 16u : 0u, pol);
                 } else {
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {

@@ -283,6 +283,7 @@ def run_cohort(args, wl):
     lane_pyr = ([torch.empty(lib.cf_corr_pyramid_bytes(b - a, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
                  for a, b in bounds] if len(bounds) > 1 else [pyramid])
     lab = torch.empty(P, 1, IH, IW, dtype=torch.int64, device=dev)
+    lane_counts = torch.zeros(len(bounds), 4, dtype=torch.int64, device=dev)
 
     def chain(u, j, a, b):
         blk = cf.CorrBlock(u["f1"][a:b], u["f2"][a:b], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
@@ -290,15 +291,15 @@ def run_cohort(args, wl):
         for k in range(ITERS):
             blk(u["coords"][k, a:b], out=outs[k, a:b])
         cf.warp(u["img"][a:b], u["flow"][a:b], out=warped[a:b])
-        lab[a:b].copy_(cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4))
+        _, cnt = cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4, out=lab[a:b], return_counts=True)
+        lane_counts[j].copy_(cnt.sum(0))                   # per-frame class areas -> the unit's totals
         return blk
 
     def compute(u, row):
         lanes.run(P, lambda j, a, b: chain(u, j, a, b))
         row[0] = outs[ITERS - 1].sum(dtype=torch.float64)
         row[1] = warped.sum(dtype=torch.float64)
-        for c in range(4):
-            row[2 + c] = (lab == c).sum()
+        row[2:6] = lane_counts.sum(0)                      # warped-label pixel counts (fused into the mask warp)
 
     with torch.no_grad():
         rows = torch.zeros(max(len(mine), 1), WIDTH, dtype=torch.float64, device=dev)

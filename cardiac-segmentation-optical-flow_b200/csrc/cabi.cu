@@ -195,7 +195,15 @@ int cf_warp2d_onehot_argmax(const float* flow, const int64_t* label, int num_cla
     CF_REQUIRE(flow && label && out, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax: null pointer");
     CF_REQUIRE(B > 0 && H > 1 && W > 1 && num_classes > 0, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax: bad shape");
     CF_REQUIRE(out != label, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax: out must not alias label");
-    return launch_warp2d_onehot_argmax(flow, label, num_classes, B, H, W, out, (cudaStream_t)stream);
+    return launch_warp2d_onehot_argmax(flow, label, num_classes, B, H, W, out, nullptr, (cudaStream_t)stream);
+}
+
+int cf_warp2d_onehot_argmax_counts(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
+                                   int64_t* out, int64_t* counts, void* stream) {
+    CF_REQUIRE(flow && label && out && counts, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_counts: null pointer");
+    CF_REQUIRE(B > 0 && H > 1 && W > 1 && num_classes > 0, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_counts: bad shape");
+    CF_REQUIRE(out != label, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_counts: out must not alias label");
+    return launch_warp2d_onehot_argmax(flow, label, num_classes, B, H, W, out, counts, (cudaStream_t)stream);
 }
 
 // ---- on-the-fly lookup (K4) --------------------------------------------------------------------------------

@@ -256,15 +256,20 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_kernel(const float* 
 // a6, tiled: same thread mapping as warp2d_tile_kernel (lane = column, two rows per thread, 3-D grid, 32-bit index math,
 // lean coordinate round trip when the coordinate is in div_small's range).  The first version spent ~280 instructions per
 // pixel on 64-bit div / mod index arithmetic (ncu: 65 % issue-slot utilisation at 30 % of HBM).
-template <bool FASTDIV>
+// COUNT: also accumulate counts[b][c] = number of pixels of image b whose warped label is c (the per-frame class areas the
+// cohort scripts derive from the warped masks): one ballot per class per warp, one global atomic per (warp, class present).
+// Whole warps stay alive in that variant (columns beyond W are predicated off instead of returning).
+template <bool FASTDIV, bool COUNT>
 __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const float* __restrict__ flow,
                                                                          const int64_t* __restrict__ label,
                                                                          int64_t* __restrict__ out, int ncls, int B, int H,
-                                                                         int W, float ry, float rx) {
+                                                                         int W, float ry, float rx,
+                                                                         unsigned long long* __restrict__ counts) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int x = blockIdx.x * kTileW + lane;
     const int y0 = blockIdx.y * kTileH + wid * 2;
-    if (x >= W || y0 >= H) return;
+    const bool xin = x < W;
+    if (y0 >= H || (!COUNT && !xin)) return;
     const unsigned HW = (unsigned)(H * W);
     const float s1y = (float)(H - 1), s1x = (float)(W - 1), hs1y = 0.5f * s1y, hs1x = 0.5f * s1x;
     const float xf = (float)x;
@@ -273,9 +278,11 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
         const float* fl = flow + (size_t)b * 2 * HW;
         const int64_t* lb = label + (size_t)b * HW;
         int64_t* ob = out + (size_t)b * HW;
+        int won[2] = {-1, -1};
 #pragma unroll
         for (int rr = 0; rr < 2; ++rr) {
             if (rr >= rows) break;
+            if (COUNT && !xin) continue;
             const int y = y0 + rr;
             const unsigned pix = (unsigned)y * (unsigned)W + (unsigned)x;
             const float py = __fadd_rn((float)y, __ldcs(fl + pix)), px = __fadd_rn(xf, __ldcs(fl + HW + pix));
@@ -308,6 +315,13 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
                 }
             }
             __stcs(reinterpret_cast<long long*>(ob + pix), (long long)best);
+            won[rr] = best;
+        }
+        if (COUNT) {
+            for (int c = 0; c < ncls; ++c) {
+                const int n = __popc(__ballot_sync(0xffffffffu, won[0] == c)) + __popc(__ballot_sync(0xffffffffu, won[1] == c));
+                if (lane == 0 && n) atomicAdd(counts + (size_t)b * ncls + c, (unsigned long long)n);
+            }
         }
     }
 }
@@ -378,16 +392,29 @@ int launch_warp2d_taps(const float* flow, int B, int H, int W, float* taps, cuda
 }
 
 int launch_warp2d_onehot_argmax(const float* flow, const int64_t* label, int ncls, int B, int H, int W,
-                                int64_t* out, cudaStream_t s) {
+                                int64_t* out, int64_t* counts, cudaStream_t s) {
     const float ry = 1.0f / (float)(H - 1), rx = 1.0f / (float)(W - 1);
+    if (counts) {
+        const int tx = cdiv(W, kTileW), ty = cdiv(H, kTileH);
+        if (!((long)H * W < (1L << 30) && ty <= 65535)) return fail(CF_ERR_UNSUPPORTED, "warp2d_onehot_argmax: counts need an image below 2^30 pixels");
+        CF_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * (size_t)B * ncls, s));
+        long gz = (4736 + (long)tx * ty - 1) / ((long)tx * ty);
+        gz = gz < 1 ? 1 : (gz > B ? B : (gz > 65535 ? 65535 : gz));
+        const dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)gz);
+        unsigned long long* cn = reinterpret_cast<unsigned long long*>(counts);
+        if (H - 1 <= 4095 && W - 1 <= 4095) warp2d_onehot_argmax_tile_kernel<true, true><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, cn);
+        else warp2d_onehot_argmax_tile_kernel<false, true><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, cn);
+        CF_CHECK_LAUNCH("warp2d_onehot_argmax_tile_kernel<count>");
+        return CF_OK;
+    }
     static const bool legacy = [] { const char* e = getenv("CF_ARGMAX_LEGACY"); return e && atoi(e) != 0; }();   // tuning knob
     const int tiles_x = cdiv(W, kTileW), tiles_y = cdiv(H, kTileH);
     if (!legacy && (long)H * W < (1L << 30) && tiles_y <= 65535) {
         long gz = (4736 + (long)tiles_x * tiles_y - 1) / ((long)tiles_x * tiles_y);
         gz = gz < 1 ? 1 : (gz > B ? B : (gz > 65535 ? 65535 : gz));
         const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)gz);
-        if (H - 1 <= 4095 && W - 1 <= 4095) warp2d_onehot_argmax_tile_kernel<true><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx);
-        else warp2d_onehot_argmax_tile_kernel<false><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx);
+        if (H - 1 <= 4095 && W - 1 <= 4095) warp2d_onehot_argmax_tile_kernel<true, false><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, nullptr);
+        else warp2d_onehot_argmax_tile_kernel<false, false><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, nullptr);
         CF_CHECK_LAUNCH("warp2d_onehot_argmax_tile_kernel");
         return CF_OK;
     }

@@ -126,6 +126,12 @@ CF_API int cf_warp2d_taps(const float* flow, int B, int H, int W, float* taps, v
  * label int64 [B,1,H,W] with values in [0, num_classes); out int64 [B,1,H,W]. */
 CF_API int cf_warp2d_onehot_argmax(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
                             int64_t* out, void* stream);
+/* Same, and counts[b][c] (int64 [B, num_classes], overwritten) = number of pixels of image b whose warped label is c:
+ * the per-frame class areas the cohort scripts take from the registered masks (`np.count_nonzero(registered == c)`
+ * patterns downstream of SegFlowGaussian.py:3571-3580), produced by the same launch instead of num_classes
+ * compare-and-reduce passes over the int64 map. */
+CF_API int cf_warp2d_onehot_argmax_counts(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
+                                   int64_t* out, int64_t* counts, void* stream);
 
 /* ---- 8(f) next rows ---------------------------------------------------------------------------------------------
  * Backward passes (autograd): gradients of the warp w.r.t. src and flow, of the lookup w.r.t. the pyramid,

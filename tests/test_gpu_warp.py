@@ -92,6 +92,28 @@ def test_onehot_argmax(golden_warp):
     assert torch.equal(out, unfused.cpu())
 
 
+@pytest.mark.parametrize("shape,ncls", [((3, 224, 224), 4), ((2, 37, 50), 4), ((5, 16, 33), 2), ((1, 96, 200), 7)])
+def test_onehot_argmax_counts(shape, ncls):
+    """cf_warp2d_onehot_argmax_counts: the label map equals the count-free entry point (and the oracle), counts equal a
+    bincount of every warped map; widths that are not a multiple of the 32-column tile exercise the predicated lanes."""
+    B, H, W = shape
+    g = torch.Generator().manual_seed(B * 1000 + W)
+    label = torch.randint(0, ncls, (B, 1, H, W), generator=g)
+    flow = torch.randn(B, 2, H, W, generator=g) * 3
+    plain = cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls)
+    buf = torch.full((B, 1, H, W), -7, dtype=torch.int64, device=DEV)
+    out, counts = cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, out=buf, return_counts=True)
+    assert out.data_ptr() == buf.data_ptr() and torch.equal(out, plain)
+    assert torch.equal(out.cpu(), warp_oracle.warp_onehot_argmax(flow, label, ncls))
+    want = torch.stack([torch.bincount(out[b].flatten().cpu(), minlength=ncls) for b in range(B)])
+    assert torch.equal(counts.cpu(), want) and int(counts.sum()) == B * H * W
+    # counts are overwritten, not accumulated, by a second call into the same storage
+    out2, counts2 = cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, return_counts=True)
+    assert torch.equal(counts2, counts)
+    with pytest.raises(ValueError):
+        cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, out=torch.empty(B, 1, H, W, device=DEV))
+
+
 def test_full_size_properties_cfg3():
     """BASELINE cfg 3 size (300 x (1+4) x 224^2): size-independent properties instead of a CPU oracle."""
     g = torch.Generator(device=DEV).manual_seed(5)

@@ -185,6 +185,48 @@ def make_utils_warp():
     print("utils_warp_reference.npz:", len(out), "arrays")
 
 
+def make_ncc():
+    """lib/loss.py:15-76 `class NCC`, compiled out of the reference file (the module imports kornia / matplotlib, absent
+    here); its hard-coded `win_size.cuda()` is a no-op for the duration of the calls.  Cases: noise, smooth (ill-conditioned
+    variances), a warped pair, borders smaller than the window, and the 5-D reduction=None branch."""
+    import ast
+    import torch.nn.functional as F
+    path = "/root/reference/nnunet/lib/loss.py"
+    tree = ast.parse(open(path).read())
+    node = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "NCC")
+    ns = {"torch": torch, "F": F, "np": np}
+    exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
+    NCC = ns["NCC"]
+    out = {}
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        def smooth(g, n, h, w):
+            z = torch.randn(n, 1, max(h // 8, 2), max(w // 8, 2), generator=g)
+            return F.interpolate(z, size=(h, w), mode="bicubic", align_corners=True) * 0.3 + 0.5
+        cases = {}
+        g = gen(6001); cases["ncc_noise_40"] = (torch.rand(2, 1, 40, 40, generator=g), torch.rand(2, 1, 40, 40, generator=g))
+        g = gen(6002); a = smooth(g, 2, 48, 37); cases["ncc_smooth_48x37"] = (a, a + 0.05 * torch.randn(2, 1, 48, 37, generator=g))
+        g = gen(6003); a = smooth(g, 1, 64, 64); cases["ncc_shift_64"] = (a, torch.roll(a, shifts=(2, -3), dims=(2, 3)))
+        g = gen(6004); cases["ncc_tiny_5x7"] = (torch.rand(3, 1, 5, 7, generator=g), torch.rand(3, 1, 5, 7, generator=g))
+        g = gen(6005); a = torch.rand(1, 1, 33, 70, generator=g); cases["ncc_same_33x70"] = (a, a.clone())
+        for name, (I, J) in cases.items():
+            out[f"{name}.I"], out[f"{name}.J"] = I.numpy(), J.numpy()
+            out[f"{name}.loss"] = NCC()(I.clone(), J.clone()).numpy()
+            T = I.shape[0]
+            out[f"{name}.map"] = NCC(reduction=None)(I.clone()[:, None], J.clone()[:, None]).numpy()     # [T,1,1,H,W]
+        # gradients of the mean loss w.r.t. both images (autograd through the reference's own expression)
+        for name in ("ncc_noise_40", "ncc_smooth_48x37"):
+            I = torch.from_numpy(out[f"{name}.I"]).clone().requires_grad_(True)
+            J = torch.from_numpy(out[f"{name}.J"]).clone().requires_grad_(True)
+            NCC()(I, J).backward()
+            out[f"{name}.gI"], out[f"{name}.gJ"] = I.grad.numpy(), J.grad.numpy()
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    np.savez_compressed(os.path.join(GOLDEN, "ncc_reference.npz"), **out)
+    print("ncc_reference.npz:", len(out), "arrays")
+
+
 def make_upsample():
     ref = load_reference_methods("/root/reference/nnunet/network_architecture/SegFlowGaussian.py",
                                  ["upsample_flow", "upsample_seg"])
@@ -210,3 +252,4 @@ if __name__ == "__main__":
     make_corr()
     make_upsample()
     make_utils_warp()
+    make_ncc()

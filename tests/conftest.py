@@ -44,6 +44,12 @@ def golden_utils_warp():
     return np.load(os.path.join(GOLDEN, "utils_warp_reference.npz"))
 
 
+@pytest.fixture(scope="session")
+def golden_ncc():
+    return np.load(os.path.join(GOLDEN, "ncc_reference.npz"))
+
+
+NCC_CASES = ["ncc_noise_40", "ncc_smooth_48x37", "ncc_shift_64", "ncc_tiny_5x7", "ncc_same_33x70"]
 UTILS_WARP_CASES = ["uw_24", "uw_17x40", "uw_oob_16", "uw_zero_12"]
 UPSAMPLE_CASES = ["u_6x5", "u_12x12", "u_9x33"]
 WARP_CASES = ["zero_24", "integer_32x40", "half_16", "noise_48", "smooth_64x48", "oob_20"]

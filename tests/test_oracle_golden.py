@@ -143,3 +143,27 @@ def test_utils_warp_restatement_matches_reference_fixture(golden_utils_warp, nam
     assert np.array_equal(got.numpy(), g[f"{name}.out"])
     if name == "uw_zero_12":      # align_corners=False: zero flow is NOT the identity (half-pixel shift towards the centre)
         assert not np.allclose(got.numpy(), g[f"{name}.x"])
+
+
+@pytest.mark.parametrize("name", ["ncc_noise_40", "ncc_smooth_48x37", "ncc_shift_64", "ncc_tiny_5x7", "ncc_same_33x70"])
+def test_ncc_restatement_matches_reference_fixture(golden_ncc, name):
+    """oracle/ncc_oracle.NCC against the reference's own lib/loss.py `NCC` (class compiled out of its file by
+    oracle/make_golden.py).  Same ATen convolutions; a multi-threaded run may differ in the last ulps of the box sums,
+    which the cancelling variance terms amplify, so the bound is the reference's own distance from float64."""
+    from oracle import ncc_oracle
+    g = golden_ncc
+    I, J = torch.from_numpy(g[f"{name}.I"]), torch.from_numpy(g[f"{name}.J"])
+    ref_map = torch.from_numpy(g[f"{name}.map"])                       # 1 - cc, [T,1,1,H,W]
+    exact = 1 - ncc_oracle.cc64(I, J)[:, None]
+    tol = max(1e-6, 4 * float((ref_map.double() - exact).abs().max()))
+    got = ncc_oracle.NCC(reduction=None)(I[:, None], J[:, None])
+    assert got.shape == ref_map.shape and float((got - ref_map).abs().max()) <= tol
+    assert abs(float(ncc_oracle.NCC()(I, J)) - float(g[f"{name}.loss"])) <= 1e-6
+    if f"{name}.gI" in g.files:
+        Ig, Jg = I.clone().requires_grad_(True), J.clone().requires_grad_(True)
+        ncc_oracle.NCC()(Ig, Jg).backward()
+        scale = float(np.abs(g[f"{name}.gI"]).max())
+        assert float((Ig.grad - torch.from_numpy(g[f"{name}.gI"])).abs().max()) <= 1e-3 * scale
+        assert float((Jg.grad - torch.from_numpy(g[f"{name}.gJ"])).abs().max()) <= 1e-3 * scale
+    with pytest.raises(ValueError):
+        ncc_oracle.NCC(reduction=None)(I, J)                           # the reference's 4-D branch has no T, B, C

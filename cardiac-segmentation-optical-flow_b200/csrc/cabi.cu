@@ -323,4 +323,31 @@ int cf_upsample_convex_bwd(const float* field, const float* mask, const float* g
     return launch_upsample_convex_bwd(field, mask, grad_out, B, C, H, W, scale, grad_field, grad_mask, (cudaStream_t)stream);
 }
 
+size_t cf_ncc_workspace_bytes(int N, int H, int W, int backward) { return ncc_workspace_bytes(N, H, W, backward); }
+
+int cf_ncc(const float* I, const float* J, int N, int H, int W, int win, float eps, float* loss_map, float* cc_sum, void* workspace,
+           size_t ws_bytes, void* stream) {
+    CF_REQUIRE(I && J, CF_ERR_BAD_ARG, "cf_ncc: null pointer");
+    CF_REQUIRE(loss_map || cc_sum, CF_ERR_BAD_ARG, "cf_ncc: neither loss_map nor cc_sum requested");
+    CF_REQUIRE(N > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_ncc: bad shape N=%d H=%d W=%d", N, H, W);
+    CF_REQUIRE(win == 9, CF_ERR_UNSUPPORTED, "cf_ncc: win %d (every NCC in the reference is built with the default 9)", win);
+    CF_REQUIRE(!cc_sum || (workspace && ws_bytes >= ncc_workspace_bytes(N, H, W, 0)), CF_ERR_BAD_ARG,
+               "cf_ncc: workspace of %zu bytes needed, got %zu", ncc_workspace_bytes(N, H, W, 0), ws_bytes);
+    CF_REQUIRE(loss_map != I && loss_map != J, CF_ERR_BAD_ARG, "cf_ncc: loss_map must not alias the inputs");
+    return launch_ncc(I, J, N, H, W, eps, loss_map, cc_sum, (float*)workspace, (cudaStream_t)stream);
+}
+
+int cf_ncc_bwd(const float* I, const float* J, int N, int H, int W, int win, float eps, const float* grad, int per_pixel, float mult,
+               float* grad_I, float* grad_J, void* workspace, size_t ws_bytes, void* stream) {
+    CF_REQUIRE(I && J && grad, CF_ERR_BAD_ARG, "cf_ncc_bwd: null pointer");
+    CF_REQUIRE(grad_I || grad_J, CF_ERR_BAD_ARG, "cf_ncc_bwd: neither grad_I nor grad_J requested");
+    CF_REQUIRE(N > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_ncc_bwd: bad shape N=%d H=%d W=%d", N, H, W);
+    CF_REQUIRE(win == 9, CF_ERR_UNSUPPORTED, "cf_ncc_bwd: win %d (every NCC in the reference is built with the default 9)", win);
+    CF_REQUIRE(workspace && ws_bytes >= ncc_workspace_bytes(N, H, W, 1), CF_ERR_BAD_ARG,
+               "cf_ncc_bwd: workspace of %zu bytes needed, got %zu", ncc_workspace_bytes(N, H, W, 1), ws_bytes);
+    CF_REQUIRE(grad_I != I && grad_I != J && grad_J != I && grad_J != J, CF_ERR_BAD_ARG,
+               "cf_ncc_bwd: gradients must not alias the inputs");
+    return launch_ncc_bwd(I, J, N, H, W, eps, grad, per_pixel, mult, grad_I, grad_J, (float*)workspace, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -179,6 +179,26 @@ CF_API int cf_upsample_convex(const float* field, const float* mask, int B, int 
 CF_API int cf_upsample_convex_bwd(const float* field, const float* mask, const float* grad_out, int B, int C, int H, int W,
                            int factor, float scale, float* grad_field, float* grad_mask, void* stream);
 
+/* Local normalised cross-correlation, the registration loss taken on the warped frame (adjacent row of SURVEY 8(f)):
+ * replaces `NCC.forward` of nnunet/lib/loss.py:15-76 (constructed at training/network_training/SegFlowGaussian.py:337,
+ * FinalFlowRaft.py:259, nnMTLTrainerV2Raft.py:275, Optical_flow_model_successive.py:71).  I, J [N,1,H,W] fp32 (the ones
+ * kernel of the reference has one input channel); five zero-padded win x win box sums, then
+ * cc = clamp(cross^2 / (I_var * J_var + eps), 0.001, 0.999).  loss_map [N,H,W] (may be NULL) receives 1 - cc (what reduction=None
+ * returns); cc_sum [1] (may be NULL) receives sum(cc) in a fixed summation order (the host forms 1 - cc_sum / (N*H*W)); workspace of
+ * cf_ncc_workspace_bytes(N, H, W, 0) bytes is needed when cc_sum is given.  Only win = 9 exists in the reference
+ * (CF_ERR_UNSUPPORTED otherwise). */
+CF_API size_t cf_ncc_workspace_bytes(int N, int H, int W, int backward);
+CF_API int cf_ncc(const float* I, const float* J, int N, int H, int W, int win, float eps, float* loss_map, float* cc_sum,
+           void* workspace, size_t ws_bytes, void* stream);
+
+/* Backward of cf_ncc (the loss is back-propagated through the warp into the flow, trainer SegFlowGaussian.py:2225).
+ * d(loss)/d(cc[p]) = mult * grad[p] when per_pixel (grad [N,H,W]: reduction=None, mult = -1 for `1 - cc`), else
+ * mult * grad[0] (grad = the scalar upstream gradient on the device: reduction='mean', mult = -1/(N*H*W)); clamped pixels
+ * pass no gradient.  grad_I / grad_J [N,1,H,W] are written (either may be NULL); workspace of
+ * cf_ncc_workspace_bytes(N, H, W, 1) bytes holds the five coefficient maps between the two launches. */
+CF_API int cf_ncc_bwd(const float* I, const float* J, int N, int H, int W, int win, float eps, const float* grad, int per_pixel,
+               float mult, float* grad_I, float* grad_J, void* workspace, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -161,3 +161,37 @@ if args.cfg == "cfg3":
     lab = [torch.randint(0, 4, (B, 1, IH, IH), device=dev) for _ in range(nrot)]
     us, mn = timeit(lambda i: cf.warp_onehot_argmax(smooth[i], lab[i]), nrot)
     report(f"onehot-argmax {B}x{IH}^2", us, mn, B * IH * IH * 24)
+    if want("ncc"):   # the registration loss on the warped frames of the same batch (lib/loss.py:15-76)
+        nrot = 4      # 2 x 60 MB per set: rotate over > L2
+        I = [torch.rand(B, 1, IH, IH, device=dev) for _ in range(nrot)]
+        J = [(I[k] + 0.05 * torch.randn(B, 1, IH, IH, device=dev)).contiguous() for k in range(nrot)]
+        npx = B * IH * IH
+        nws = lib.cf_ncc_workspace_bytes(B, IH, IH, 0)
+        ws = torch.empty(nws // 4 + 1, device=dev)
+        omap = torch.empty(B, 1, IH, IH, device=dev)
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_ncc(I[i].data_ptr(), J[i].data_ptr(), B, IH, IH, 9, 1e-3, None,
+                                                          ws[nws // 4:].data_ptr(), ws.data_ptr(), nws, _cabi.stream())), nrot)
+        report(f"ncc mean {B}x{IH}^2", us, mn, 8 * npx)
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_ncc(I[i].data_ptr(), J[i].data_ptr(), B, IH, IH, 9, 1e-3, omap.data_ptr(),
+                                                          None, None, 0, _cabi.stream())), nrot)
+        report(f"ncc map {B}x{IH}^2", us, mn, 12 * npx)
+        bws = torch.empty(5 * npx, device=dev)
+        g1 = torch.ones(1, device=dev)
+        gI, gJ = torch.empty_like(I[0]), torch.empty_like(I[0])
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_ncc_bwd(I[i].data_ptr(), J[i].data_ptr(), B, IH, IH, 9, 1e-3, g1.data_ptr(), 0,
+                                                              -1.0 / npx, gI.data_ptr(), gJ.data_ptr(), bws.data_ptr(), 20 * npx,
+                                                              _cabi.stream())), nrot)
+        report(f"ncc backward (2 launches) {B}x{IH}^2", us, mn, 16 * npx)
+        import torch.nn.functional as F
+        wones = torch.ones(1, 1, 9, 9, device=dev)
+
+        def aten_ncc(i):    # the reference's formulation on ATen CUDA kernels (5 conv2d + elementwise), for scale only
+            a, b = I[i], J[i]
+            s = [F.conv2d(t, wones, padding=4) for t in (a, b, a * a, b * b, a * b)]
+            uI, uJ = s[0] / 81.0, s[1] / 81.0
+            cross = s[4] - uJ * s[0] - uI * s[1] + uI * uJ * 81.0
+            iv = s[2] - 2 * uI * s[0] + uI * uI * 81.0
+            jv = s[3] - 2 * uJ * s[1] + uJ * uJ * 81.0
+            return 1 - torch.clamp(cross * cross / (iv * jv + 1e-3), 0.001, 0.999).mean()
+        us, mn = timeit(aten_ncc, nrot, reps=10)
+        report(f"(ATen conv2d formulation, same GPU) {B}x{IH}^2", us, mn, 8 * npx)

@@ -2,27 +2,35 @@
 // /root/reference/nnunet/lib/loss.py:15-76 (five zero-padded 9x9 box sums of I, J, I*I, J*J, I*J through conv2d with a
 // ones kernel, then cc = clamp(cross^2 / (I_var * J_var + eps), 0.001, 0.999)) and its autograd.
 //
-// One skeleton, three instantiations (box5_kernel<Load, Epi>): a warp owns a strip of 32 input columns and walks down the
-// rows; a lane loads one pixel per row (coalesced 128 B per warp and array), the horizontal 9-sum of the five quantities is
-// a log-step shuffle chain (v+1, +2, +4, +8: 4 shuffles per quantity, valid on lanes 0..23), the vertical 9-sum runs over a
-// register ring of the last nine row sums (statically indexed: the row loop is unrolled by 9).  Nothing is staged in shared
-// memory and no intermediate box sum ever reaches HBM.
+// One skeleton, three instantiations (box5_walk<Load, Epi>).  A warp owns a strip of 128 input columns (a lane = 4
+// consecutive columns, one 128-bit load per array and row) and walks down a band of rows:
+//   vertical   : running 9-row sums of the five quantities in registers (add the entering row, subtract the leaving one,
+//                which is re-read through L1; both rows are fetched one iteration ahead of their use),
+//   horizontal : a lane's four 9-sums need its own 4 columns, the total of the next lane and three prefixes + the total of
+//                the lane after that: 5 shuffles per quantity per 4 pixels (a lane-per-pixel log-step chain costs 16),
+//   epilogue   : per-pixel arithmetic on the five box sums, 128-bit stores.  120 of 128 columns produce outputs.
+// Nothing is staged in shared memory and no intermediate box sum ever reaches HBM.
 //   forward : Load = (I-cI, J-cJ and their products), Epi = cc -> optional map of 1 - cc + per-task partial sum of cc
 //   bwd A   : same Load, Epi = the five coefficient maps a, b, c, m1, m2 of d(loss)/d(box sums) (workspace [5,N,H,W])
 //   bwd B   : Load = the five maps (zero outside the image: the adjoint of a zero-padded box filter is the same box
 //             filter), Epi = gI = J*A + 2*I*B - M1, gJ = I*A + 2*J*C - M2
 // Pivot: the variance terms cancel catastrophically in fp32 (I2_sum ~ 81*mean^2 against I_var ~ 81*var).  cross, I_var and
 // J_var are invariant under I -> I - cI, J -> J - cJ when the zero padding is shifted too, so every task subtracts the
-// pixel at its centre (padding becomes -c): the same formula, evaluated closer to the float64 value than the reference's
-// own fp32 evaluation (tests bound both by their distance from float64).
+// pixel at its centre (padding becomes -c) and evaluates the algebraically identical cross = IJ_sum - I_sum*J_sum/n,
+// I_var = I2_sum - I_sum^2/n on the shifted sums: closer to the float64 value than the reference's own fp32 evaluation
+// (tests bound both by their distance from float64).
+#include <initializer_list>
+
 #include "common.cuh"
 
 namespace cf {
 namespace {
 
-constexpr int kWin = 9, kHalo = 4, kOutCols = 32 - 2 * kHalo;   // 24 output columns per warp strip
-constexpr int kRows = 56;                                       // output rows per task (8 priming rows: 12.5 % overhead)
-constexpr int kWarps = 4;
+constexpr int kWin = 9, kHalo = 4;
+constexpr int kInCols = 128, kOutCols = kInCols - 2 * kHalo;   // 120 output columns per warp strip (lanes 0..29)
+constexpr int kRows = 16;                                      // output rows per task (+9 priming rows of adds only)
+constexpr int kWarps = 1;   // one warp per CTA: the task is a function of blockIdx alone, so the compiler sees the row loop as
+                            // warp-uniform and emits plain SHFLs (with 4 warps per CTA every shuffle carried a divergence check)
 
 struct Task {
     int n, y0, x0, rows;   // image, first output row / column, output rows of this task
@@ -42,111 +50,170 @@ __device__ __forceinline__ Task decode_task(long t, int H, int W) {
     return k;
 }
 
-struct V5 {
-    float v[5];
+struct Q5 {
+    float v[5][4];   // quantity, column
 };
 
-__device__ __forceinline__ V5 hsum9(const V5& a) {
-    V5 r;
-#pragma unroll
-    for (int i = 0; i < 5; ++i) {
-        const float s2 = a.v[i] + __shfl_down_sync(0xffffffffu, a.v[i], 1);
-        const float s4 = s2 + __shfl_down_sync(0xffffffffu, s2, 2);
-        const float s8 = s4 + __shfl_down_sync(0xffffffffu, s4, 4);
-        r.v[i] = s8 + __shfl_down_sync(0xffffffffu, a.v[i], 8);
+// 4 consecutive floats of row y starting at column x (x % 4 == 0 when vec), `pad` outside the image
+// Branch-free: the address is clamped into the image and the value selected afterwards, so the warp stays converged
+// around the shuffles and the loads can be hoisted a whole iteration ahead.
+template <bool VEC>
+__device__ __forceinline__ float4 load4(const float* img, int y, int x, int H, int W, float pad) {
+    const bool row_in = (unsigned)y < (unsigned)H;
+    const float* row = img + (long)min(max(y, 0), H - 1) * W;
+    float4 r;
+    if (VEC) {
+        r = __ldg(reinterpret_cast<const float4*>(row + min(max(x, 0), W - 4)));
+        if (!(row_in && (unsigned)x < (unsigned)W)) r = make_float4(pad, pad, pad, pad);
+    } else {
+        const float e0 = __ldg(row + min(max(x + 0, 0), W - 1)), e1 = __ldg(row + min(max(x + 1, 0), W - 1));
+        const float e2 = __ldg(row + min(max(x + 2, 0), W - 1)), e3 = __ldg(row + min(max(x + 3, 0), W - 1));
+        r.x = (row_in && (unsigned)(x + 0) < (unsigned)W) ? e0 : pad;
+        r.y = (row_in && (unsigned)(x + 1) < (unsigned)W) ? e1 : pad;
+        r.z = (row_in && (unsigned)(x + 2) < (unsigned)W) ? e2 : pad;
+        r.w = (row_in && (unsigned)(x + 3) < (unsigned)W) ? e3 : pad;
     }
     return r;
 }
-
-// Load(y, x) -> five values of input pixel (y, x) (any y, x: the functor handles the padding);
-// Epi(y, x, sums) for every in-image output pixel of the task.
-template <class Load, class Epi>
-__device__ __forceinline__ void box5_walk(const Task& k, int W, Load& load, Epi& epi) {
-    const int lane = threadIdx.x & 31;
-    const int xin = k.x0 - kHalo + lane;          // input column of this lane
-    const int xout = k.x0 + lane;                 // output column (window start = xin, centre = xin + 4)
-    const bool live = lane < kOutCols && xout < W;
-    V5 ring[kWin];
+template <bool VEC>
+__device__ __forceinline__ void store4(float* img, int y, int x, int W, const float (&o)[4]) {
+    float* row = img + (long)y * W;
+    if (VEC) {
+        *reinterpret_cast<float4*>(row + x) = make_float4(o[0], o[1], o[2], o[3]);
+    } else {
 #pragma unroll
-    for (int j = 0; j < kWin - 1; ++j) ring[j] = hsum9(load(k.y0 - kHalo + j, xin));
-    for (int y = 0; y < k.rows; y += kWin) {
-#pragma unroll
-        for (int j = 0; j < kWin; ++j) {
-            if (y + j < k.rows) {                 // warp-uniform
-                ring[(kWin - 1 + j) % kWin] = hsum9(load(k.y0 + y + j + kHalo, xin));
-                V5 s;
-#pragma unroll
-                for (int i = 0; i < 5; ++i) {
-                    float acc = ring[0].v[i];
-#pragma unroll
-                    for (int q = 1; q < kWin; ++q) acc += ring[q].v[i];
-                    s.v[i] = acc;
-                }
-                if (live) epi(k.y0 + y + j, xout, s);
-            }
-        }
+        for (int c = 0; c < 4; ++c)
+            if (x + c < W) row[x + c] = o[c];
     }
 }
 
+// horizontal 9-sums of a lane's four windows (window c starts at the lane's column c); valid on lanes 0..29
+__device__ __forceinline__ void hsum9x4(const float (&v)[4], float (&o)[4]) {
+    const float p2 = v[0] + v[1], s23 = v[2] + v[3];
+    const float p3 = p2 + v[2], s123 = v[1] + s23, t = p2 + s23;
+    const float T1 = __shfl_down_sync(0xffffffffu, t, 1);
+    const float T2 = __shfl_down_sync(0xffffffffu, t, 2);
+    const float P1 = __shfl_down_sync(0xffffffffu, v[0], 2);
+    const float P2 = __shfl_down_sync(0xffffffffu, p2, 2);
+    const float P3 = __shfl_down_sync(0xffffffffu, p3, 2);
+    o[0] = (t + T1) + P1;
+    o[1] = (s123 + T1) + P2;
+    o[2] = (s23 + T1) + P3;
+    o[3] = (v[3] + T1) + T2;
+}
+
+// Load: Raw fetch(y) (this lane's 4 columns of row y, any y) and accumulate(V, raw, sign).
+// Epi(y, x, sums) for the 4 output pixels (y, x..x+3) of a lane; x < W is guaranteed, x + c < W is the functor's business.
+template <class Load, class Epi>
+__device__ __forceinline__ void box5_walk(const Task& k, int W, const Load& load, Epi& epi) {
+    const int lane = threadIdx.x & 31;
+    const int xout = k.x0 + 4 * lane;             // first output column of this lane (its windows start at xout - 4)
+    const bool live = lane < kOutCols / 4 && xout < W;
+    Q5 V;
+#pragma unroll
+    for (int q = 0; q < 5; ++q)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) V.v[q][c] = 0.f;
+    // rows y0-5 .. y0+3: the window of output row y0 - 1 (row y0-5 leaves in the first iteration)
+#pragma unroll 3
+    for (int j = -kHalo - 1; j < kHalo; ++j) load.accumulate(V, load.fetch(k.y0 + j), 1.0f);
+    typename Load::Raw enter = load.fetch(k.y0 + kHalo), leave = load.fetch(k.y0 - kHalo - 1);
+    for (int y = k.y0; y < k.y0 + k.rows; ++y) {
+        const typename Load::Raw e = enter, l = leave;
+        enter = load.fetch(y + 1 + kHalo);        // next iteration's rows: in flight while this row is computed
+        leave = load.fetch(y - kHalo);
+        load.accumulate(V, e, 1.0f);
+        load.accumulate(V, l, -1.0f);
+        Q5 S;
+#pragma unroll
+        for (int q = 0; q < 5; ++q) hsum9x4(V.v[q], S.v[q]);
+        if (live) epi(y, xout, S);
+    }
+}
+
+template <bool VEC>
 struct PairLoad {   // (I - cI, J - cJ, squares, product); padding = (0 - c)
+    struct Raw {
+        float4 a, b;
+    };
     const float *I, *J;
-    int H, W;
+    int H, W, x;     // x = this lane's first input column
     float cI, cJ;
-    __device__ __forceinline__ V5 operator()(int y, int x) const {
-        float a = -cI, b = -cJ;
-        if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
-            a = __ldg(I + (long)y * W + x) - cI;
-            b = __ldg(J + (long)y * W + x) - cJ;
+    __device__ __forceinline__ Raw fetch(int y) const {
+        return Raw{load4<VEC>(I, y, x, H, W, 0.f), load4<VEC>(J, y, x, H, W, 0.f)};
+    }
+    __device__ __forceinline__ void accumulate(Q5& V, const Raw& r, float sign) const {
+        const float a[4] = {r.a.x - cI, r.a.y - cI, r.a.z - cI, r.a.w - cI};
+        const float b[4] = {r.b.x - cJ, r.b.y - cJ, r.b.z - cJ, r.b.w - cJ};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float sa = sign * a[c], sb = sign * b[c];
+            V.v[0][c] += sa;
+            V.v[1][c] += sb;
+            V.v[2][c] = fmaf(sa, a[c], V.v[2][c]);
+            V.v[3][c] = fmaf(sb, b[c], V.v[3][c]);
+            V.v[4][c] = fmaf(sa, b[c], V.v[4][c]);
         }
-        V5 r;
-        r.v[0] = a; r.v[1] = b; r.v[2] = a * a; r.v[3] = b * b; r.v[4] = a * b;
-        return r;
     }
 };
 
-struct Stats {   // loss.py:59-66 on (shifted) sums
+struct Stats {   // loss.py:59-66 on shifted sums: cross = IJ - Is*Js/n, I_var = I2 - Is^2/n (same algebra, fewer roundings)
     float uI, uJ, cross, Iv, Jv, D, cc0;
 };
-__device__ __forceinline__ Stats stats_of(const V5& s, float eps) {
-    const float n = (float)(kWin * kWin);
+__device__ __forceinline__ Stats stats_of(const Q5& s, int c, float eps) {
+    const float inv_n = 1.0f / (float)(kWin * kWin);
     Stats t;
-    t.uI = __fdiv_rn(s.v[0], n);
-    t.uJ = __fdiv_rn(s.v[1], n);
-    t.cross = s.v[4] - t.uJ * s.v[0] - t.uI * s.v[1] + t.uI * t.uJ * n;
-    t.Iv = s.v[2] - 2.0f * t.uI * s.v[0] + t.uI * t.uI * n;
-    t.Jv = s.v[3] - 2.0f * t.uJ * s.v[1] + t.uJ * t.uJ * n;
-    t.D = t.Iv * t.Jv + eps;
-    t.cc0 = __fdiv_rn(t.cross * t.cross, t.D);
+    t.uI = s.v[0][c] * inv_n;
+    t.uJ = s.v[1][c] * inv_n;
+    t.cross = fmaf(-t.uI, s.v[1][c], s.v[4][c]);
+    t.Iv = fmaf(-t.uI, s.v[0][c], s.v[2][c]);
+    t.Jv = fmaf(-t.uJ, s.v[1][c], s.v[3][c]);
+    t.D = fmaf(t.Iv, t.Jv, eps);
+    t.cc0 = __fdividef(t.cross * t.cross, t.D);
     return t;
 }
 
+// Pivot = the task's centre pixel scaled by the in-image fraction of the task's input footprint: ~ the mean of the windows
+// INCLUDING their zero padding (an interior task subtracts the pixel itself, a 3x3 image whose windows are 8/9 padding
+// subtracts almost nothing).  Any pivot gives the same result in exact arithmetic; this one keeps the shifted sums small.
 __device__ __forceinline__ void task_pivot(const float* I, const float* J, const Task& k, int H, int W, float* cI, float* cJ) {
-    const long p = (long)min(k.y0 + k.rows / 2, H - 1) * W + min(k.x0 + kOutCols / 2, W - 1);
-    *cI = __ldg(I + p);
-    *cJ = __ldg(J + p);
+    const int cols = min(kOutCols, W - k.x0);
+    const long p = (long)min(k.y0 + k.rows / 2, H - 1) * W + min(k.x0 + cols / 2, W - 1);
+    const int in_rows = min(H, k.y0 + k.rows + kHalo) - max(0, k.y0 - kHalo);
+    const int in_cols = min(W, k.x0 + cols + kHalo) - max(0, k.x0 - kHalo);
+    const float f = (float)(in_rows * in_cols) / (float)((k.rows + 2 * kHalo) * (cols + 2 * kHalo));
+    *cI = f * __ldg(I + p);
+    *cJ = f * __ldg(J + p);
 }
 
+template <bool VEC>
 struct FwdEpi {
     float* map;   // image base or nullptr
     int W;
     float eps, acc;
-    __device__ __forceinline__ void operator()(int y, int x, const V5& s) {
-        const float cc = fminf(fmaxf(stats_of(s, eps).cc0, 0.001f), 0.999f);
-        if (map) map[(long)y * W + x] = 1.0f - cc;             // what reduction=None returns (loss.py:76)
-        acc += cc;
+    __device__ __forceinline__ void operator()(int y, int x, const Q5& s) {
+        float o[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float cc = fminf(fmaxf(stats_of(s, c, eps).cc0, 0.001f), 0.999f);
+            o[c] = 1.0f - cc;                      // what reduction=None returns (loss.py:76)
+            if (x + c < W) acc += cc;
+        }
+        if (map) store4<VEC>(map, y, x, W, o);
     }
 };
 
+template <bool VEC>
 __global__ void __launch_bounds__(kWarps * 32) ncc_fwd_kernel(const float* __restrict__ I, const float* __restrict__ J, int H, int W,
                                                              long n_tasks, float eps, float* __restrict__ loss_map,
                                                              float* __restrict__ partial) {
-    const long t = (long)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const long t = blockIdx.x;
     if (t >= n_tasks) return;
     const Task k = decode_task(t, H, W);
     const long img = (long)k.n * H * W;
-    PairLoad load{I + img, J + img, H, W, 0.f, 0.f};
+    PairLoad<VEC> load{I + img, J + img, H, W, k.x0 - kHalo + 4 * (int)(threadIdx.x & 31), 0.f, 0.f};
     task_pivot(load.I, load.J, k, H, W, &load.cI, &load.cJ);
-    FwdEpi epi{loss_map ? loss_map + img : nullptr, W, eps, 0.f};
+    FwdEpi<VEC> epi{loss_map ? loss_map + img : nullptr, W, eps, 0.f};
     box5_walk(k, W, load, epi);
     float a = epi.acc;
 #pragma unroll
@@ -168,89 +235,124 @@ __global__ void __launch_bounds__(256) ncc_reduce_kernel(const float* __restrict
     if (threadIdx.x == 0) *cc_sum = (float)sh[0];
 }
 
+template <bool VEC>
 struct CoefEpi {   // d(loss)/d(box sums) folded into five maps
     float* ws;     // [5, N, H, W] base + image offset
     const float* gpix;   // per-pixel upstream (image base) or nullptr
     long plane;    // N*H*W
-    int W;
+    int H, W;
     float eps, gscale, cI, cJ;
-    __device__ __forceinline__ void operator()(int y, int x, const V5& s) {
-        const Stats t = stats_of(s, eps);
-        const long p = (long)y * W + x;
-        float w = gscale;
-        if (gpix) w *= gpix[p];
-        if (!(t.cc0 >= 0.001f && t.cc0 <= 0.999f)) w = 0.f;          // clamp passes gradient on the closed interval
-        const float invD = __fdiv_rn(1.0f, t.D);
-        const float a = w * 2.0f * t.cross * invD;
-        const float q = -w * t.cross * t.cross * invD * invD;
-        const float b = q * t.Jv, c = q * t.Iv;
-        const float uI = t.uI + cI, uJ = t.uJ + cJ;                   // absolute means: pass B multiplies absolute pixels
-        ws[p] = a;
-        ws[plane + p] = b;
-        ws[2 * plane + p] = c;
-        ws[3 * plane + p] = a * uJ + 2.0f * b * uI;
-        ws[4 * plane + p] = a * uI + 2.0f * c * uJ;
+    __device__ __forceinline__ void operator()(int y, int x, const Q5& s) {
+        float g[4] = {1.f, 1.f, 1.f, 1.f};
+        if (gpix) {
+            const float4 u = load4<VEC>(gpix, y, x, H, W, 0.f);
+            g[0] = u.x; g[1] = u.y; g[2] = u.z; g[3] = u.w;
+        }
+        float m[5][4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const Stats t = stats_of(s, c, eps);
+            float w = gscale * g[c];
+            if (!(t.cc0 >= 0.001f && t.cc0 <= 0.999f)) w = 0.f;      // clamp passes gradient on the closed interval
+            const float invD = __fdividef(1.0f, t.D);
+            const float a = w * 2.0f * t.cross * invD;
+            const float q = -w * t.cross * t.cross * invD * invD;
+            const float b = q * t.Jv, cc = q * t.Iv;
+            const float uI = t.uI + cI, uJ = t.uJ + cJ;               // absolute means: pass B multiplies absolute pixels
+            m[0][c] = a;
+            m[1][c] = b;
+            m[2][c] = cc;
+            m[3][c] = fmaf(a, uJ, 2.0f * b * uI);
+            m[4][c] = fmaf(a, uI, 2.0f * cc * uJ);
+        }
+#pragma unroll
+        for (int q = 0; q < 5; ++q) store4<VEC>(ws + q * plane, y, x, W, m[q]);
     }
 };
 
+template <bool VEC>
 __global__ void __launch_bounds__(kWarps * 32) ncc_bwd_coef_kernel(const float* __restrict__ I, const float* __restrict__ J, int N, int H,
-                                                                  int W, long n_tasks, float eps, const float* __restrict__ grad,
-                                                                  int per_pixel, float mult, float* __restrict__ ws) {
-    const long t = (long)blockIdx.x * kWarps + (threadIdx.x >> 5);
+                                                                  int W, long n_tasks, float eps,
+                                                                  const float* __restrict__ grad, int per_pixel, float mult,
+                                                                  float* __restrict__ ws) {
+    const long t = blockIdx.x;
     if (t >= n_tasks) return;
     const Task k = decode_task(t, H, W);
     const long img = (long)k.n * H * W;
-    PairLoad load{I + img, J + img, H, W, 0.f, 0.f};
+    PairLoad<VEC> load{I + img, J + img, H, W, k.x0 - kHalo + 4 * (int)(threadIdx.x & 31), 0.f, 0.f};
     task_pivot(load.I, load.J, k, H, W, &load.cI, &load.cJ);
-    CoefEpi epi{ws + img, per_pixel ? grad + img : nullptr, (long)N * H * W, W, eps,
+    CoefEpi<VEC> epi{ws + img, per_pixel ? grad + img : nullptr, (long)N * H * W, H, W, eps,
                 per_pixel ? mult : mult * __ldg(grad), load.cI, load.cJ};
     box5_walk(k, W, load, epi);
 }
 
+template <bool VEC>
 struct MapLoad {
+    struct Raw {
+        float4 m[5];
+    };
     const float* ws;   // image base of map 0
     long plane;
-    int H, W;
-    __device__ __forceinline__ V5 operator()(int y, int x) const {
-        V5 r;
-        if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
-            const long p = (long)y * W + x;
+    int H, W, x;
+    __device__ __forceinline__ Raw fetch(int y) const {
+        Raw r;
 #pragma unroll
-            for (int i = 0; i < 5; ++i) r.v[i] = __ldg(ws + i * plane + p);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 5; ++i) r.v[i] = 0.f;
-        }
+        for (int q = 0; q < 5; ++q) r.m[q] = load4<VEC>(ws + q * plane, y, x, H, W, 0.f);
         return r;
+    }
+    __device__ __forceinline__ void accumulate(Q5& V, const Raw& r, float sign) const {
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            V.v[q][0] = fmaf(sign, r.m[q].x, V.v[q][0]);
+            V.v[q][1] = fmaf(sign, r.m[q].y, V.v[q][1]);
+            V.v[q][2] = fmaf(sign, r.m[q].z, V.v[q][2]);
+            V.v[q][3] = fmaf(sign, r.m[q].w, V.v[q][3]);
+        }
     }
 };
 
+template <bool VEC>
 struct GradEpi {
     const float *I, *J;
     float *gI, *gJ;   // image bases or nullptr
-    int W;
-    __device__ __forceinline__ void operator()(int y, int x, const V5& s) {
-        const long p = (long)y * W + x;
-        const float i = __ldg(I + p), j = __ldg(J + p);
-        if (gI) gI[p] = j * s.v[0] + 2.0f * i * s.v[1] - s.v[3];
-        if (gJ) gJ[p] = i * s.v[0] + 2.0f * j * s.v[2] - s.v[4];
+    int H, W;
+    __device__ __forceinline__ void operator()(int y, int x, const Q5& s) {
+        const float4 i4 = load4<VEC>(I, y, x, H, W, 0.f), j4 = load4<VEC>(J, y, x, H, W, 0.f);
+        const float i[4] = {i4.x, i4.y, i4.z, i4.w}, j[4] = {j4.x, j4.y, j4.z, j4.w};
+        float oi[4], oj[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            oi[c] = fmaf(j[c], s.v[0][c], fmaf(2.0f * i[c], s.v[1][c], -s.v[3][c]));
+            oj[c] = fmaf(i[c], s.v[0][c], fmaf(2.0f * j[c], s.v[2][c], -s.v[4][c]));
+        }
+        if (gI) store4<VEC>(gI, y, x, W, oi);
+        if (gJ) store4<VEC>(gJ, y, x, W, oj);
     }
 };
 
+template <bool VEC>
 __global__ void __launch_bounds__(kWarps * 32) ncc_bwd_gather_kernel(const float* __restrict__ I, const float* __restrict__ J, int N, int H,
                                                                     int W, long n_tasks, const float* __restrict__ ws,
                                                                     float* __restrict__ gI, float* __restrict__ gJ) {
-    const long t = (long)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const long t = blockIdx.x;
     if (t >= n_tasks) return;
     const Task k = decode_task(t, H, W);
     const long img = (long)k.n * H * W;
-    MapLoad load{ws + img, (long)N * H * W, H, W};
-    GradEpi epi{I + img, J + img, gI ? gI + img : nullptr, gJ ? gJ + img : nullptr, W};
+    MapLoad<VEC> load{ws + img, (long)N * H * W, H, W, k.x0 - kHalo + 4 * (int)(threadIdx.x & 31)};
+    GradEpi<VEC> epi{I + img, J + img, gI ? gI + img : nullptr, gJ ? gJ + img : nullptr, H, W};
     box5_walk(k, W, load, epi);
 }
 
 long task_count(int N, int H, int W) {
     return (long)N * ((H + kRows - 1) / kRows) * ((W + kOutCols - 1) / kOutCols);
+}
+
+// 128-bit loads / stores need rows that start on 16-byte boundaries
+bool vec_ok(int W, std::initializer_list<const void*> ptrs) {
+    if (W % 4) return false;
+    for (const void* p : ptrs)
+        if (p && !aligned16(p)) return false;
+    return true;
 }
 
 }  // namespace
@@ -263,7 +365,10 @@ size_t ncc_workspace_bytes(int N, int H, int W, int backward) {
 int launch_ncc(const float* I, const float* J, int N, int H, int W, float eps, float* loss_map, float* cc_sum, float* partial,
                cudaStream_t s) {
     const long nt = task_count(N, H, W);
-    ncc_fwd_kernel<<<cdiv(nt, kWarps), kWarps * 32, 0, s>>>(I, J, H, W, nt, eps, loss_map, cc_sum ? partial : nullptr);
+    const int vec = vec_ok(W, {I, J, loss_map});
+    const dim3 grid(cdiv(nt, kWarps)), block(kWarps * 32);
+    if (vec) ncc_fwd_kernel<true><<<grid, block, 0, s>>>(I, J, H, W, nt, eps, loss_map, cc_sum ? partial : nullptr);
+    else ncc_fwd_kernel<false><<<grid, block, 0, s>>>(I, J, H, W, nt, eps, loss_map, cc_sum ? partial : nullptr);
     CF_CHECK_LAUNCH("ncc_fwd_kernel");
     if (cc_sum) {
         ncc_reduce_kernel<<<1, 256, 0, s>>>(partial, nt, cc_sum);
@@ -275,9 +380,13 @@ int launch_ncc(const float* I, const float* J, int N, int H, int W, float eps, f
 int launch_ncc_bwd(const float* I, const float* J, int N, int H, int W, float eps, const float* grad, int per_pixel, float mult,
                    float* gI, float* gJ, float* ws, cudaStream_t s) {
     const long nt = task_count(N, H, W);
-    ncc_bwd_coef_kernel<<<cdiv(nt, kWarps), kWarps * 32, 0, s>>>(I, J, N, H, W, nt, eps, grad, per_pixel, mult, ws);
+    const int vec = vec_ok(W, {I, J, gI, gJ, ws, per_pixel ? grad : nullptr}) && ((size_t)N * H * W) % 4 == 0;
+    const dim3 grid(cdiv(nt, kWarps)), block(kWarps * 32);
+    if (vec) ncc_bwd_coef_kernel<true><<<grid, block, 0, s>>>(I, J, N, H, W, nt, eps, grad, per_pixel, mult, ws);
+    else ncc_bwd_coef_kernel<false><<<grid, block, 0, s>>>(I, J, N, H, W, nt, eps, grad, per_pixel, mult, ws);
     CF_CHECK_LAUNCH("ncc_bwd_coef_kernel");
-    ncc_bwd_gather_kernel<<<cdiv(nt, kWarps), kWarps * 32, 0, s>>>(I, J, N, H, W, nt, ws, gI, gJ);
+    if (vec) ncc_bwd_gather_kernel<true><<<grid, block, 0, s>>>(I, J, N, H, W, nt, ws, gI, gJ);
+    else ncc_bwd_gather_kernel<false><<<grid, block, 0, s>>>(I, J, N, H, W, nt, ws, gI, gJ);
     CF_CHECK_LAUNCH("ncc_bwd_gather_kernel");
     return CF_OK;
 }

@@ -13,7 +13,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr",
     "-I", os.path.join(ROOT, "include"), "-I", CSRC,
-]
+] + os.environ.get("CF_NVCC_EXTRA", "").split()      # development knobs (-DNCC_ROWS=.. etc.); empty in every shipped build
 
 
 def sources():

@@ -28,7 +28,13 @@ namespace {
 
 constexpr int kWin = 9, kHalo = 4;
 constexpr int kInCols = 128, kOutCols = kInCols - 2 * kHalo;   // 120 output columns per warp strip (lanes 0..29)
-constexpr int kRows = 16;                                      // output rows per task (+9 priming rows of adds only)
+#ifndef NCC_ROWS
+#define NCC_ROWS 16
+#endif
+#ifndef NCC_MINB
+#define NCC_MINB 1
+#endif
+constexpr int kRows = NCC_ROWS;                                // output rows per task (+9 priming rows of adds only)
 constexpr int kWarps = 1;   // one warp per CTA: the task is a function of blockIdx alone, so the compiler sees the row loop as
                             // warp-uniform and emits plain SHFLs (with 4 warps per CTA every shuffle carried a divergence check)
 
@@ -50,9 +56,11 @@ __device__ __forceinline__ Task decode_task(long t, int H, int W) {
     return k;
 }
 
-struct Q5 {
-    float v[5][4];   // quantity, column
+template <int NQ>
+struct QN {
+    float v[NQ][4];   // quantity, column
 };
+using Q5 = QN<5>;
 
 // 4 consecutive floats of row y starting at column x (x % 4 == 0 when vec), `pad` outside the image
 // Branch-free: the address is clamped into the image and the value selected afterwards, so the warp stays converged
@@ -109,9 +117,10 @@ __device__ __forceinline__ void box5_walk(const Task& k, int W, const Load& load
     const int lane = threadIdx.x & 31;
     const int xout = k.x0 + 4 * lane;             // first output column of this lane (its windows start at xout - 4)
     const bool live = lane < kOutCols / 4 && xout < W;
-    Q5 V;
+    constexpr int NQ = Load::kNQ;
+    QN<NQ> V;
 #pragma unroll
-    for (int q = 0; q < 5; ++q)
+    for (int q = 0; q < NQ; ++q)
 #pragma unroll
         for (int c = 0; c < 4; ++c) V.v[q][c] = 0.f;
     // rows y0-5 .. y0+3: the window of output row y0 - 1 (row y0-5 leaves in the first iteration)
@@ -124,15 +133,16 @@ __device__ __forceinline__ void box5_walk(const Task& k, int W, const Load& load
         leave = load.fetch(y - kHalo);
         load.accumulate(V, e, 1.0f);
         load.accumulate(V, l, -1.0f);
-        Q5 S;
+        QN<NQ> S;
 #pragma unroll
-        for (int q = 0; q < 5; ++q) hsum9x4(V.v[q], S.v[q]);
+        for (int q = 0; q < NQ; ++q) hsum9x4(V.v[q], S.v[q]);
         if (live) epi(y, xout, S);
     }
 }
 
 template <bool VEC>
 struct PairLoad {   // (I - cI, J - cJ, squares, product); padding = (0 - c)
+    static constexpr int kNQ = 5;
     struct Raw {
         float4 a, b;
     };
@@ -204,7 +214,7 @@ struct FwdEpi {
 };
 
 template <bool VEC>
-__global__ void __launch_bounds__(kWarps * 32) ncc_fwd_kernel(const float* __restrict__ I, const float* __restrict__ J, int H, int W,
+__global__ void __launch_bounds__(kWarps * 32, NCC_MINB) ncc_fwd_kernel(const float* __restrict__ I, const float* __restrict__ J, int H, int W,
                                                              long n_tasks, float eps, float* __restrict__ loss_map,
                                                              float* __restrict__ partial) {
     const long t = blockIdx.x;
@@ -222,33 +232,42 @@ __global__ void __launch_bounds__(kWarps * 32) ncc_fwd_kernel(const float* __res
 }
 
 // fixed-order sum of the per-task partials in double: the loss does not depend on scheduling
-__global__ void __launch_bounds__(256) ncc_reduce_kernel(const float* __restrict__ partial, long n, float* __restrict__ cc_sum) {
-    __shared__ double sh[256];
+__global__ void __launch_bounds__(1024) ncc_reduce_kernel(const float* __restrict__ partial, long n, float* __restrict__ cc_sum) {
+    __shared__ double sh[1024];
     double a = 0.0;
-    for (long i = threadIdx.x; i < n; i += 256) a += (double)partial[i];
+#pragma unroll 4
+    for (long i = threadIdx.x; i < n; i += 1024) a += (double)partial[i];
     sh[threadIdx.x] = a;
     __syncthreads();
-    for (int o = 128; o; o >>= 1) {
+    for (int o = 512; o; o >>= 1) {
         if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
         __syncthreads();
     }
     if (threadIdx.x == 0) *cc_sum = (float)sh[0];
 }
 
-template <bool VEC>
-struct CoefEpi {   // d(loss)/d(box sums) folded into five maps
-    float* ws;     // [5, N, H, W] base + image offset
+// MODE 0: both gradients (maps a, b, c, m1, m2); 1: grad_I only (a, b, m1); 2: grad_J only (a, c, m2) -- the usual case in
+// training, where only the warped frame carries a gradient: 3 maps instead of 5 through HBM and through the second box filter.
+template <int MODE>
+struct BwdMaps {
+    static constexpr int kNQ = MODE == 0 ? 5 : 3;
+};
+
+template <bool VEC, int MODE>
+struct CoefEpi {   // d(loss)/d(box sums) folded into kNQ maps
+    float* ws;     // [kNQ, N, H, W] base + image offset
     const float* gpix;   // per-pixel upstream (image base) or nullptr
     long plane;    // N*H*W
     int H, W;
     float eps, gscale, cI, cJ;
     __device__ __forceinline__ void operator()(int y, int x, const Q5& s) {
+        constexpr int NQ = BwdMaps<MODE>::kNQ;
         float g[4] = {1.f, 1.f, 1.f, 1.f};
         if (gpix) {
             const float4 u = load4<VEC>(gpix, y, x, H, W, 0.f);
             g[0] = u.x; g[1] = u.y; g[2] = u.z; g[3] = u.w;
         }
-        float m[5][4];
+        float m[NQ][4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             const Stats t = stats_of(s, c, eps);
@@ -260,18 +279,26 @@ struct CoefEpi {   // d(loss)/d(box sums) folded into five maps
             const float b = q * t.Jv, cc = q * t.Iv;
             const float uI = t.uI + cI, uJ = t.uJ + cJ;               // absolute means: pass B multiplies absolute pixels
             m[0][c] = a;
-            m[1][c] = b;
-            m[2][c] = cc;
-            m[3][c] = fmaf(a, uJ, 2.0f * b * uI);
-            m[4][c] = fmaf(a, uI, 2.0f * cc * uJ);
+            if (MODE == 0) {
+                m[1][c] = b;
+                m[2][c] = cc;
+                m[3][c] = fmaf(a, uJ, 2.0f * b * uI);
+                m[4][c] = fmaf(a, uI, 2.0f * cc * uJ);
+            } else if (MODE == 1) {
+                m[1][c] = b;
+                m[2][c] = fmaf(a, uJ, 2.0f * b * uI);
+            } else {
+                m[1][c] = cc;
+                m[2][c] = fmaf(a, uI, 2.0f * cc * uJ);
+            }
         }
 #pragma unroll
-        for (int q = 0; q < 5; ++q) store4<VEC>(ws + q * plane, y, x, W, m[q]);
+        for (int q = 0; q < NQ; ++q) store4<VEC>(ws + q * plane, y, x, W, m[q]);
     }
 };
 
-template <bool VEC>
-__global__ void __launch_bounds__(kWarps * 32) ncc_bwd_coef_kernel(const float* __restrict__ I, const float* __restrict__ J, int N, int H,
+template <bool VEC, int MODE>
+__global__ void __launch_bounds__(kWarps * 32, NCC_MINB) ncc_bwd_coef_kernel(const float* __restrict__ I, const float* __restrict__ J, int N, int H,
                                                                   int W, long n_tasks, float eps,
                                                                   const float* __restrict__ grad, int per_pixel, float mult,
                                                                   float* __restrict__ ws) {
@@ -281,15 +308,16 @@ __global__ void __launch_bounds__(kWarps * 32) ncc_bwd_coef_kernel(const float* 
     const long img = (long)k.n * H * W;
     PairLoad<VEC> load{I + img, J + img, H, W, k.x0 - kHalo + 4 * (int)(threadIdx.x & 31), 0.f, 0.f};
     task_pivot(load.I, load.J, k, H, W, &load.cI, &load.cJ);
-    CoefEpi<VEC> epi{ws + img, per_pixel ? grad + img : nullptr, (long)N * H * W, H, W, eps,
+    CoefEpi<VEC, MODE> epi{ws + img, per_pixel ? grad + img : nullptr, (long)N * H * W, H, W, eps,
                 per_pixel ? mult : mult * __ldg(grad), load.cI, load.cJ};
     box5_walk(k, W, load, epi);
 }
 
-template <bool VEC>
+template <bool VEC, int MODE>
 struct MapLoad {
+    static constexpr int kNQ = BwdMaps<MODE>::kNQ;
     struct Raw {
-        float4 m[5];
+        float4 m[kNQ];
     };
     const float* ws;   // image base of map 0
     long plane;
@@ -297,12 +325,12 @@ struct MapLoad {
     __device__ __forceinline__ Raw fetch(int y) const {
         Raw r;
 #pragma unroll
-        for (int q = 0; q < 5; ++q) r.m[q] = load4<VEC>(ws + q * plane, y, x, H, W, 0.f);
+        for (int q = 0; q < kNQ; ++q) r.m[q] = load4<VEC>(ws + q * plane, y, x, H, W, 0.f);
         return r;
     }
-    __device__ __forceinline__ void accumulate(Q5& V, const Raw& r, float sign) const {
+    __device__ __forceinline__ void accumulate(QN<kNQ>& V, const Raw& r, float sign) const {
 #pragma unroll
-        for (int q = 0; q < 5; ++q) {
+        for (int q = 0; q < kNQ; ++q) {
             V.v[q][0] = fmaf(sign, r.m[q].x, V.v[q][0]);
             V.v[q][1] = fmaf(sign, r.m[q].y, V.v[q][1]);
             V.v[q][2] = fmaf(sign, r.m[q].z, V.v[q][2]);
@@ -311,35 +339,41 @@ struct MapLoad {
     }
 };
 
-template <bool VEC>
+template <bool VEC, int MODE>
 struct GradEpi {
     const float *I, *J;
-    float *gI, *gJ;   // image bases or nullptr
+    float *gI, *gJ;   // image bases (MODE 1: gJ unused, MODE 2: gI unused)
     int H, W;
-    __device__ __forceinline__ void operator()(int y, int x, const Q5& s) {
+    __device__ __forceinline__ void operator()(int y, int x, const QN<BwdMaps<MODE>::kNQ>& s) {
         const float4 i4 = load4<VEC>(I, y, x, H, W, 0.f), j4 = load4<VEC>(J, y, x, H, W, 0.f);
         const float i[4] = {i4.x, i4.y, i4.z, i4.w}, j[4] = {j4.x, j4.y, j4.z, j4.w};
         float oi[4], oj[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            oi[c] = fmaf(j[c], s.v[0][c], fmaf(2.0f * i[c], s.v[1][c], -s.v[3][c]));
-            oj[c] = fmaf(i[c], s.v[0][c], fmaf(2.0f * j[c], s.v[2][c], -s.v[4][c]));
+            if (MODE == 0) {
+                oi[c] = fmaf(j[c], s.v[0][c], fmaf(2.0f * i[c], s.v[1][c], -s.v[3][c]));
+                oj[c] = fmaf(i[c], s.v[0][c], fmaf(2.0f * j[c], s.v[2][c], -s.v[4][c]));
+            } else if (MODE == 1) {
+                oi[c] = fmaf(j[c], s.v[0][c], fmaf(2.0f * i[c], s.v[1][c], -s.v[2][c]));
+            } else {
+                oj[c] = fmaf(i[c], s.v[0][c], fmaf(2.0f * j[c], s.v[1][c], -s.v[2][c]));
+            }
         }
-        if (gI) store4<VEC>(gI, y, x, W, oi);
-        if (gJ) store4<VEC>(gJ, y, x, W, oj);
+        if (MODE != 2) store4<VEC>(gI, y, x, W, oi);
+        if (MODE != 1) store4<VEC>(gJ, y, x, W, oj);
     }
 };
 
-template <bool VEC>
-__global__ void __launch_bounds__(kWarps * 32) ncc_bwd_gather_kernel(const float* __restrict__ I, const float* __restrict__ J, int N, int H,
+template <bool VEC, int MODE>
+__global__ void __launch_bounds__(kWarps * 32, NCC_MINB) ncc_bwd_gather_kernel(const float* __restrict__ I, const float* __restrict__ J, int N, int H,
                                                                     int W, long n_tasks, const float* __restrict__ ws,
                                                                     float* __restrict__ gI, float* __restrict__ gJ) {
     const long t = blockIdx.x;
     if (t >= n_tasks) return;
     const Task k = decode_task(t, H, W);
     const long img = (long)k.n * H * W;
-    MapLoad<VEC> load{ws + img, (long)N * H * W, H, W, k.x0 - kHalo + 4 * (int)(threadIdx.x & 31)};
-    GradEpi<VEC> epi{I + img, J + img, gI ? gI + img : nullptr, gJ ? gJ + img : nullptr, H, W};
+    MapLoad<VEC, MODE> load{ws + img, (long)N * H * W, H, W, k.x0 - kHalo + 4 * (int)(threadIdx.x & 31)};
+    GradEpi<VEC, MODE> epi{I + img, J + img, gI ? gI + img : nullptr, gJ ? gJ + img : nullptr, H, W};
     box5_walk(k, W, load, epi);
 }
 
@@ -371,24 +405,32 @@ int launch_ncc(const float* I, const float* J, int N, int H, int W, float eps, f
     else ncc_fwd_kernel<false><<<grid, block, 0, s>>>(I, J, H, W, nt, eps, loss_map, cc_sum ? partial : nullptr);
     CF_CHECK_LAUNCH("ncc_fwd_kernel");
     if (cc_sum) {
-        ncc_reduce_kernel<<<1, 256, 0, s>>>(partial, nt, cc_sum);
+        ncc_reduce_kernel<<<1, 1024, 0, s>>>(partial, nt, cc_sum);
         CF_CHECK_LAUNCH("ncc_reduce_kernel");
     }
     return CF_OK;
 }
 
-int launch_ncc_bwd(const float* I, const float* J, int N, int H, int W, float eps, const float* grad, int per_pixel, float mult,
-                   float* gI, float* gJ, float* ws, cudaStream_t s) {
+template <bool VEC, int MODE>
+int launch_ncc_bwd_t(const float* I, const float* J, int N, int H, int W, float eps, const float* grad, int per_pixel, float mult,
+                     float* gI, float* gJ, float* ws, cudaStream_t s) {
     const long nt = task_count(N, H, W);
-    const int vec = vec_ok(W, {I, J, gI, gJ, ws, per_pixel ? grad : nullptr}) && ((size_t)N * H * W) % 4 == 0;
     const dim3 grid(cdiv(nt, kWarps)), block(kWarps * 32);
-    if (vec) ncc_bwd_coef_kernel<true><<<grid, block, 0, s>>>(I, J, N, H, W, nt, eps, grad, per_pixel, mult, ws);
-    else ncc_bwd_coef_kernel<false><<<grid, block, 0, s>>>(I, J, N, H, W, nt, eps, grad, per_pixel, mult, ws);
+    ncc_bwd_coef_kernel<VEC, MODE><<<grid, block, 0, s>>>(I, J, N, H, W, nt, eps, grad, per_pixel, mult, ws);
     CF_CHECK_LAUNCH("ncc_bwd_coef_kernel");
-    if (vec) ncc_bwd_gather_kernel<true><<<grid, block, 0, s>>>(I, J, N, H, W, nt, ws, gI, gJ);
-    else ncc_bwd_gather_kernel<false><<<grid, block, 0, s>>>(I, J, N, H, W, nt, ws, gI, gJ);
+    ncc_bwd_gather_kernel<VEC, MODE><<<grid, block, 0, s>>>(I, J, N, H, W, nt, ws, gI, gJ);
     CF_CHECK_LAUNCH("ncc_bwd_gather_kernel");
     return CF_OK;
+}
+
+int launch_ncc_bwd(const float* I, const float* J, int N, int H, int W, float eps, const float* grad, int per_pixel, float mult,
+                   float* gI, float* gJ, float* ws, cudaStream_t s) {
+    const bool vec = vec_ok(W, {I, J, gI, gJ, ws, per_pixel ? grad : nullptr});
+    const int mode = (gI && gJ) ? 0 : (gI ? 1 : 2);
+#define CF_NCC_BWD(V, M) launch_ncc_bwd_t<V, M>(I, J, N, H, W, eps, grad, per_pixel, mult, gI, gJ, ws, s)
+    if (vec) return mode == 0 ? CF_NCC_BWD(true, 0) : (mode == 1 ? CF_NCC_BWD(true, 1) : CF_NCC_BWD(true, 2));
+    return mode == 0 ? CF_NCC_BWD(false, 0) : (mode == 1 ? CF_NCC_BWD(false, 1) : CF_NCC_BWD(false, 2));
+#undef CF_NCC_BWD
 }
 
 }  // namespace cf

@@ -89,6 +89,14 @@ def test_backward_against_autograd_of_the_oracle(shape, mean):
     for got, want in ((Ig.grad, Id.grad), (Jg.grad, Jd.grad)):
         scale = float(want.abs().max())
         assert float((got.cpu().double() - want).abs().max()) <= 1e-3 * scale
+    # single-gradient launches (3 coefficient maps instead of 5) give the same numbers as the two-gradient launch
+    for which in (0, 1):
+        a, b = I.cuda().requires_grad_(which == 0), J.cuda().requires_grad_(which == 1)
+        out = cf.NCC()(a, b) if mean else (cf.NCC(reduction=None)(a[None], b[None]) * up.cuda()).sum()
+        out.backward()
+        one, both = (a.grad, Ig.grad) if which == 0 else (b.grad, Jg.grad)
+        assert (a.grad is None) != (b.grad is None)
+        assert float((one - both).abs().max()) <= 1e-5 * float(both.abs().max())
 
 
 def test_only_one_gradient_and_identical_images():

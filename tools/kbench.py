@@ -181,7 +181,11 @@ if args.cfg == "cfg3":
         us, mn = timeit(lambda i: _cabi.check(lib.cf_ncc_bwd(I[i].data_ptr(), J[i].data_ptr(), B, IH, IH, 9, 1e-3, g1.data_ptr(), 0,
                                                               -1.0 / npx, gI.data_ptr(), gJ.data_ptr(), bws.data_ptr(), 20 * npx,
                                                               _cabi.stream())), nrot)
-        report(f"ncc backward (2 launches) {B}x{IH}^2", us, mn, 16 * npx)
+        report(f"ncc backward, both grads (2 launches) {B}x{IH}^2", us, mn, 16 * npx)
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_ncc_bwd(I[i].data_ptr(), J[i].data_ptr(), B, IH, IH, 9, 1e-3, g1.data_ptr(), 0,
+                                                              -1.0 / npx, None, gJ.data_ptr(), bws.data_ptr(), 20 * npx,
+                                                              _cabi.stream())), nrot)
+        report(f"ncc backward, grad_J only (2 launches) {B}x{IH}^2", us, mn, 12 * npx)
         import torch.nn.functional as F
         wones = torch.ones(1, 1, 9, 9, device=dev)
 

@@ -62,6 +62,39 @@ struct QN {
 };
 using Q5 = QN<5>;
 
+// sm_100a packed fp32: one instruction for two IEEE round-to-nearest operations on an aligned register pair
+// (FADD2 / FMUL2 / FFMA2 in SASS).  The kernels are issue-bound, so halving the instruction count of the element-wise
+// stretches (pivot subtraction, vertical accumulation, per-pixel statistics) is what pays.
+struct F2 {
+    unsigned long long u;
+};
+__device__ __forceinline__ F2 pk(float lo, float hi) {
+    F2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r.u) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk(F2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.u)); }
+__device__ __forceinline__ F2 add2(F2 a, F2 b) {
+    F2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u));
+    return r;
+}
+__device__ __forceinline__ F2 sub2(F2 a, F2 b) {
+    F2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u));
+    return r;
+}
+__device__ __forceinline__ F2 mul2(F2 a, F2 b) {
+    F2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u));
+    return r;
+}
+__device__ __forceinline__ F2 fma2(F2 a, F2 b, F2 c) {
+    F2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.u) : "l"(a.u), "l"(b.u), "l"(c.u));
+    return r;
+}
+
 // 4 consecutive floats of row y starting at column x (x % 4 == 0 when vec), `pad` outside the image
 // Branch-free: the address is clamped into the image and the value selected afterwards, so the warp stays converged
 // around the shuffles and the loads can be hoisted a whole iteration ahead.
@@ -152,35 +185,53 @@ struct PairLoad {   // (I - cI, J - cJ, squares, product); padding = (0 - c)
     __device__ __forceinline__ Raw fetch(int y) const {
         return Raw{load4<VEC>(I, y, x, H, W, 0.f), load4<VEC>(J, y, x, H, W, 0.f)};
     }
+    // sign = +1: the row enters the window; -1: it leaves (products are negated through the (c - x) form, no extra multiply)
     __device__ __forceinline__ void accumulate(Q5& V, const Raw& r, float sign) const {
-        const float a[4] = {r.a.x - cI, r.a.y - cI, r.a.z - cI, r.a.w - cI};
-        const float b[4] = {r.b.x - cJ, r.b.y - cJ, r.b.z - cJ, r.b.w - cJ};
+        const F2 c_i = pk(cI, cI), c_j = pk(cJ, cJ);
+        const F2 ra[2] = {pk(r.a.x, r.a.y), pk(r.a.z, r.a.w)}, rb[2] = {pk(r.b.x, r.b.y), pk(r.b.z, r.b.w)};
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float sa = sign * a[c], sb = sign * b[c];
-            V.v[0][c] += sa;
-            V.v[1][c] += sb;
-            V.v[2][c] = fmaf(sa, a[c], V.v[2][c]);
-            V.v[3][c] = fmaf(sb, b[c], V.v[3][c]);
-            V.v[4][c] = fmaf(sa, b[c], V.v[4][c]);
+        for (int h = 0; h < 2; ++h) {
+            const F2 a = sub2(ra[h], c_i), b = sub2(rb[h], c_j);
+            const F2 sa = sign > 0.f ? a : sub2(c_i, ra[h]), sb = sign > 0.f ? b : sub2(c_j, rb[h]);
+            F2 v0 = pk(V.v[0][2 * h], V.v[0][2 * h + 1]), v1 = pk(V.v[1][2 * h], V.v[1][2 * h + 1]);
+            F2 v2 = pk(V.v[2][2 * h], V.v[2][2 * h + 1]), v3 = pk(V.v[3][2 * h], V.v[3][2 * h + 1]);
+            F2 v4 = pk(V.v[4][2 * h], V.v[4][2 * h + 1]);
+            v0 = add2(v0, sa);
+            v1 = add2(v1, sb);
+            v2 = fma2(sa, a, v2);
+            v3 = fma2(sb, b, v3);
+            v4 = fma2(sa, b, v4);
+            upk(v0, V.v[0][2 * h], V.v[0][2 * h + 1]);
+            upk(v1, V.v[1][2 * h], V.v[1][2 * h + 1]);
+            upk(v2, V.v[2][2 * h], V.v[2][2 * h + 1]);
+            upk(v3, V.v[3][2 * h], V.v[3][2 * h + 1]);
+            upk(v4, V.v[4][2 * h], V.v[4][2 * h + 1]);
         }
     }
 };
 
 struct Stats {   // loss.py:59-66 on shifted sums: cross = IJ - Is*Js/n, I_var = I2 - Is^2/n (same algebra, fewer roundings)
-    float uI, uJ, cross, Iv, Jv, D, cc0;
+    float nuI, nuJ, cross, Iv, Jv, D, cc0;   // nuI = -I_sum/n (the negated mean: feeds the FFMA2s without a negation)
 };
-__device__ __forceinline__ Stats stats_of(const Q5& s, int c, float eps) {
-    const float inv_n = 1.0f / (float)(kWin * kWin);
-    Stats t;
-    t.uI = s.v[0][c] * inv_n;
-    t.uJ = s.v[1][c] * inv_n;
-    t.cross = fmaf(-t.uI, s.v[1][c], s.v[4][c]);
-    t.Iv = fmaf(-t.uI, s.v[0][c], s.v[2][c]);
-    t.Jv = fmaf(-t.uJ, s.v[1][c], s.v[3][c]);
-    t.D = fmaf(t.Iv, t.Jv, eps);
-    t.cc0 = __fdividef(t.cross * t.cross, t.D);
-    return t;
+// statistics of the column pair (2h, 2h+1) with packed arithmetic
+__device__ __forceinline__ void stats_pair(const Q5& s, int h, float eps, Stats (&t)[2]) {
+    const float ninv = -1.0f / (float)(kWin * kWin);
+    const F2 S0 = pk(s.v[0][2 * h], s.v[0][2 * h + 1]), S1 = pk(s.v[1][2 * h], s.v[1][2 * h + 1]);
+    const F2 S2 = pk(s.v[2][2 * h], s.v[2][2 * h + 1]), S3 = pk(s.v[3][2 * h], s.v[3][2 * h + 1]);
+    const F2 S4 = pk(s.v[4][2 * h], s.v[4][2 * h + 1]);
+    const F2 nuI = mul2(S0, pk(ninv, ninv)), nuJ = mul2(S1, pk(ninv, ninv));
+    const F2 cross = fma2(nuI, S1, S4), Iv = fma2(nuI, S0, S2), Jv = fma2(nuJ, S1, S3);
+    const F2 D = fma2(Iv, Jv, pk(eps, eps)), num = mul2(cross, cross);
+    float n0, n1;
+    upk(nuI, t[0].nuI, t[1].nuI);
+    upk(nuJ, t[0].nuJ, t[1].nuJ);
+    upk(cross, t[0].cross, t[1].cross);
+    upk(Iv, t[0].Iv, t[1].Iv);
+    upk(Jv, t[0].Jv, t[1].Jv);
+    upk(D, t[0].D, t[1].D);
+    upk(num, n0, n1);
+    t[0].cc0 = __fdividef(n0, t[0].D);
+    t[1].cc0 = __fdividef(n1, t[1].D);
 }
 
 // Pivot = the task's centre pixel scaled by the in-image fraction of the task's input footprint: ~ the mean of the windows
@@ -204,10 +255,16 @@ struct FwdEpi {
     __device__ __forceinline__ void operator()(int y, int x, const Q5& s) {
         float o[4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float cc = fminf(fmaxf(stats_of(s, c, eps).cc0, 0.001f), 0.999f);
-            o[c] = 1.0f - cc;                      // what reduction=None returns (loss.py:76)
-            if (x + c < W) acc += cc;
+        for (int h = 0; h < 2; ++h) {
+            Stats t[2];
+            stats_pair(s, h, eps, t);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int c = 2 * h + e;
+                const float cc = fminf(fmaxf(t[e].cc0, 0.001f), 0.999f);
+                o[c] = 1.0f - cc;                  // what reduction=None returns (loss.py:76)
+                if (VEC || x + c < W) acc += cc;
+            }
         }
         if (map) store4<VEC>(map, y, x, W, o);
     }
@@ -268,16 +325,24 @@ struct CoefEpi {   // d(loss)/d(box sums) folded into kNQ maps
             g[0] = u.x; g[1] = u.y; g[2] = u.z; g[3] = u.w;
         }
         float m[NQ][4];
+        Stats st[4];
+        {
+            Stats t2[2];
+            stats_pair(s, 0, eps, t2);
+            st[0] = t2[0]; st[1] = t2[1];
+            stats_pair(s, 1, eps, t2);
+            st[2] = t2[0]; st[3] = t2[1];
+        }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            const Stats t = stats_of(s, c, eps);
+            const Stats t = st[c];
             float w = gscale * g[c];
             if (!(t.cc0 >= 0.001f && t.cc0 <= 0.999f)) w = 0.f;      // clamp passes gradient on the closed interval
             const float invD = __fdividef(1.0f, t.D);
             const float a = w * 2.0f * t.cross * invD;
             const float q = -w * t.cross * t.cross * invD * invD;
             const float b = q * t.Jv, cc = q * t.Iv;
-            const float uI = t.uI + cI, uJ = t.uJ + cJ;               // absolute means: pass B multiplies absolute pixels
+            const float uI = cI - t.nuI, uJ = cJ - t.nuJ;             // absolute means: pass B multiplies absolute pixels
             m[0][c] = a;
             if (MODE == 0) {
                 m[1][c] = b;
@@ -331,10 +396,10 @@ struct MapLoad {
     __device__ __forceinline__ void accumulate(QN<kNQ>& V, const Raw& r, float sign) const {
 #pragma unroll
         for (int q = 0; q < kNQ; ++q) {
-            V.v[q][0] = fmaf(sign, r.m[q].x, V.v[q][0]);
-            V.v[q][1] = fmaf(sign, r.m[q].y, V.v[q][1]);
-            V.v[q][2] = fmaf(sign, r.m[q].z, V.v[q][2]);
-            V.v[q][3] = fmaf(sign, r.m[q].w, V.v[q][3]);
+            const F2 lo = pk(r.m[q].x, r.m[q].y), hi = pk(r.m[q].z, r.m[q].w);
+            const F2 v01 = pk(V.v[q][0], V.v[q][1]), v23 = pk(V.v[q][2], V.v[q][3]);
+            upk(sign > 0.f ? add2(v01, lo) : sub2(v01, lo), V.v[q][0], V.v[q][1]);
+            upk(sign > 0.f ? add2(v23, hi) : sub2(v23, hi), V.v[q][2], V.v[q][3]);
         }
     }
 };

@@ -107,7 +107,7 @@ def test_only_one_gradient_and_identical_images():
     loss = cf.NCC()(I, J)                       # cc = var^2 / (var^2 + eps) everywhere
     loss.backward()
     assert J.grad is not None and torch.isfinite(J.grad).all()
-    assert 0.0 < float(loss) < 1.0
+    assert 0.0 < float(loss.detach()) < 1.0
     flat = torch.full((1, 1, 20, 30), 0.25, device="cuda")
     with torch.no_grad():
         m = cf.NCC(reduction=None)(flat[None], flat[None])
@@ -133,3 +133,43 @@ def test_errors_and_cabi_contract():
     assert lib.cf_ncc(a.data_ptr(), a.data_ptr(), 2, 16, 16, 9, 1e-3, None, out.data_ptr(), None, 0, None) == _cabi.CF_ERR_BAD_ARG
     assert b"workspace" in lib.cf_last_error()
     assert lib.cf_ncc_workspace_bytes(2, 16, 16, 1) == 5 * 2 * 16 * 16 * 4
+
+
+@pytest.mark.parametrize("shape", [(2, 40, 44), (3, 17, 23), (1, 5, 7), (2, 33, 128)])
+def test_outputs_stay_inside_their_buffers(shape):
+    """Guard words around every output (map, partial sums, coefficient maps, gradients) stay untouched: vector path
+    (W % 4 == 0) and element-wise path, strips and bands that end inside the image."""
+    from cardioflow_b200 import _cabi
+    lib = _cabi.lib()
+    n, h, w = shape
+    npx = n * h * w
+    gen = torch.Generator().manual_seed(w)
+    I, J = torch.rand(n, 1, h, w, generator=gen).cuda(), torch.rand(n, 1, h, w, generator=gen).cuda()
+    G = 64                                               # guard floats on both sides (keeps 16-byte alignment)
+
+    def guarded(count):
+        buf = torch.full((count + 2 * G,), 12345.0, device="cuda")
+        return buf, buf[G:G + count]
+
+    def intact(buf, count):
+        return bool((buf[:G] == 12345.0).all()) and bool((buf[G + count:] == 12345.0).all())
+
+    nws = lib.cf_ncc_workspace_bytes(n, h, w, 0) // 4
+    mbuf, m = guarded(npx)
+    pbuf, part = guarded(nws)
+    sbuf, csum = guarded(4)
+    _cabi.check(lib.cf_ncc(I.data_ptr(), J.data_ptr(), n, h, w, 9, 1e-3, m.data_ptr(), csum.data_ptr(), part.data_ptr(), nws * 4,
+                           _cabi.stream()))
+    torch.cuda.synchronize()
+    assert intact(mbuf, npx) and intact(pbuf, nws) and intact(sbuf, 4)
+    assert bool((sbuf[G + 1:G + 4] == 12345.0).all()) and not bool((m == 12345.0).any())
+    wbuf, ws = guarded(5 * npx)
+    ibuf, gi = guarded(npx)
+    jbuf, gj = guarded(npx)
+    up = torch.randn(npx, generator=gen).cuda()
+    for gI, gJ in ((gi, gj), (gi, None), (None, gj)):
+        _cabi.check(lib.cf_ncc_bwd(I.data_ptr(), J.data_ptr(), n, h, w, 9, 1e-3, up.data_ptr(), 1, -1.0,
+                                   gI.data_ptr() if gI is not None else None, gJ.data_ptr() if gJ is not None else None,
+                                   ws.data_ptr(), 5 * npx * 4, _cabi.stream()))
+        torch.cuda.synchronize()
+        assert intact(wbuf, 5 * npx) and intact(ibuf, npx) and intact(jbuf, npx)

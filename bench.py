@@ -284,6 +284,7 @@ def run_cohort(args, wl):
                  for a, b in bounds] if len(bounds) > 1 else [pyramid])
     lab = torch.empty(P, 1, IH, IW, dtype=torch.int64, device=dev)
     lane_counts = torch.zeros(len(bounds), 4, dtype=torch.int64, device=dev)
+    sum_ws = torch.empty(lib.cf_sum_f64_workspace_bytes() // 8, dtype=torch.float64, device=dev)
 
     def chain(u, j, a, b):
         blk = cf.CorrBlock(u["f1"][a:b], u["f2"][a:b], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
@@ -297,8 +298,8 @@ def run_cohort(args, wl):
 
     def compute(u, row):
         lanes.run(P, lambda j, a, b: chain(u, j, a, b))
-        row[0] = outs[ITERS - 1].sum(dtype=torch.float64)
-        row[1] = warped.sum(dtype=torch.float64)
+        shard.sum_f64(outs[ITERS - 1], row[0:1], sum_ws)     # one pass, fixed summation order (cf_sum_f64)
+        shard.sum_f64(warped, row[1:2], sum_ws)
         row[2:6] = lane_counts.sum(0)                      # warped-label pixel counts (fused into the mask warp)
 
     with torch.no_grad():
@@ -372,7 +373,7 @@ def run_cohort(args, wl):
             "clocks": clocks, "compute_ms_max_rank": compute_ms, "gather_ms_max_rank": gather_ms,
             "gather": {"collective": "all_gather_into_tensor (NCCL)" if world > 1 else "none (1 rank)",
                        "bytes_per_rank": int(rows[:len(mine)].numel() * 8), "rows_verified_on_rank0": check},
-            "gpu_launches": len(mine) * (2 + ITERS + 2) * len(bounds),
+            "gpu_launches": len(mine) * ((2 + ITERS + 2) * len(bounds) + 4),   # + two cf_sum_f64 (2 launches each)
         }
         if not all(check):
             line["error"] = "gathered rows differ from a local recomputation"

@@ -49,6 +49,8 @@ _SIGNATURES = {
     "cf_warp2d_xy_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_upsample_convex": (_I, [_P, _P, _I, _I, _I, _I, _I, _c.c_float, _P, _P]),
     "cf_upsample_convex_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _c.c_float, _P, _P, _P]),
+    "cf_sum_f64_workspace_bytes": (_Z, []),
+    "cf_sum_f64": (_I, [_P, _Z, _P, _P, _Z, _P]),
     "cf_ncc_workspace_bytes": (_Z, [_I, _I, _I, _I]),
     "cf_ncc": (_I, [_P, _P, _I, _I, _I, _I, _c.c_float, _P, _P, _P, _Z, _P]),
     "cf_ncc_bwd": (_I, [_P, _P, _I, _I, _I, _I, _c.c_float, _P, _I, _c.c_float, _P, _P, _P, _Z, _P]),

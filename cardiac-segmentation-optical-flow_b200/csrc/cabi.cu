@@ -350,4 +350,14 @@ int cf_ncc_bwd(const float* I, const float* J, int N, int H, int W, int win, flo
     return launch_ncc_bwd(I, J, N, H, W, eps, grad, per_pixel, mult, grad_I, grad_J, (float*)workspace, (cudaStream_t)stream);
 }
 
+size_t cf_sum_f64_workspace_bytes(void) { return sum_f64_workspace_bytes(); }
+
+int cf_sum_f64(const float* x, size_t n, double* out, void* workspace, size_t ws_bytes, void* stream) {
+    CF_REQUIRE(x && out, CF_ERR_BAD_ARG, "cf_sum_f64: null pointer");
+    CF_REQUIRE(aligned16(x), CF_ERR_BAD_ARG, "cf_sum_f64: x must be 16-byte aligned");
+    CF_REQUIRE(workspace && ws_bytes >= sum_f64_workspace_bytes(), CF_ERR_BAD_ARG, "cf_sum_f64: workspace of %zu bytes needed, got %zu",
+               sum_f64_workspace_bytes(), ws_bytes);
+    return launch_sum_f64(x, n, out, (double*)workspace, (cudaStream_t)stream);
+}
+
 }  // extern "C"

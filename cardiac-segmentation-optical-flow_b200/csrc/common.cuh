@@ -131,6 +131,9 @@ int launch_ncc(const float* I, const float* J, int N, int H, int W, float eps, f
 int launch_ncc_bwd(const float* I, const float* J, int N, int H, int W, float eps, const float* grad, int per_pixel, float mult,
                    float* gI, float* gJ, float* ws, cudaStream_t s);
 
+size_t sum_f64_workspace_bytes();
+int launch_sum_f64(const float* x, size_t n, double* out, double* partial, cudaStream_t s);
+
 // pooled-fmap2 pyramid of the on-the-fly lookup: level l = [B, C, h_l, w_l], 256-byte aligned offsets
 bool fmap_level_dims(int B, int C, int H, int W, int L, LevelDims* d);
 int launch_fmap_pyramid(const float* f2, int B, int C, int H, int W, int L, float* f2pyr, cudaStream_t s);

@@ -269,11 +269,17 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
     const int x = blockIdx.x * kTileW + lane;
     const int y0 = blockIdx.y * kTileH + wid * 2;
     const bool xin = x < W;
-    if (y0 >= H || (!COUNT && !xin)) return;
+    if (!COUNT && (y0 >= H || !xin)) return;      // COUNT: the whole CTA stays alive for the barriers of the count flush
+    __shared__ unsigned cta_cnt[32];               // COUNT, ncls <= 32: per-CTA class counts, one global atomic per class and image
+    const bool cta_agg = COUNT && ncls <= 32;
+    if (cta_agg) {
+        if (threadIdx.x < 32) cta_cnt[threadIdx.x] = 0u;
+        __syncthreads();
+    }
     const unsigned HW = (unsigned)(H * W);
     const float s1y = (float)(H - 1), s1x = (float)(W - 1), hs1y = 0.5f * s1y, hs1x = 0.5f * s1x;
     const float xf = (float)x;
-    const int rows = (y0 + 1 < H) ? 2 : 1;
+    const int rows = y0 >= H ? 0 : ((y0 + 1 < H) ? 2 : 1);
     for (unsigned b = blockIdx.z; b < (unsigned)B; b += gridDim.z) {
         const float* fl = flow + (size_t)b * 2 * HW;
         const int64_t* lb = label + (size_t)b * HW;
@@ -320,7 +326,19 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
         if (COUNT) {
             for (int c = 0; c < ncls; ++c) {
                 const int n = __popc(__ballot_sync(0xffffffffu, won[0] == c)) + __popc(__ballot_sync(0xffffffffu, won[1] == c));
-                if (lane == 0 && n) atomicAdd(counts + (size_t)b * ncls + c, (unsigned long long)n);
+                if (lane == 0 && n) {
+                    if (cta_agg) atomicAdd(&cta_cnt[c], (unsigned)n);
+                    else atomicAdd(counts + (size_t)b * ncls + c, (unsigned long long)n);
+                }
+            }
+            if (cta_agg) {      // 8 warps -> one global atomic per class present in this CTA's tile (was: one per warp)
+                __syncthreads();
+                if (threadIdx.x < ncls) {
+                    const unsigned n = cta_cnt[threadIdx.x];
+                    cta_cnt[threadIdx.x] = 0u;
+                    if (n) atomicAdd(counts + (size_t)b * ncls + threadIdx.x, (unsigned long long)n);
+                }
+                __syncthreads();
             }
         }
     }

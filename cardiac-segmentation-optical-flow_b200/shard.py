@@ -50,6 +50,24 @@ def gather_results(local, n_units_total, rank=None, world_size=None, group=None)
     return out[:n_units_total].contiguous()
 
 
+def sum_f64(x, out, workspace=None):
+    """Deterministic float64 sum of the fp32 CUDA tensor ``x`` into the 1-element float64 tensor / view ``out`` (cf_sum_f64):
+    one pass over ``x`` instead of ATen's cast copy + reduction, and a summation order that depends on ``x.numel()`` alone, so
+    a unit's result row is bit-identical wherever it is recomputed.  Stream-ordered, capturable."""
+    from . import _cabi
+    _cabi.require_cuda(x, out)
+    if x.dtype != torch.float32 or not x.is_contiguous() or out.dtype != torch.float64 or out.numel() != 1:
+        raise ValueError("sum_f64: x must be a contiguous float32 tensor and out a 1-element float64 tensor")
+    lib = _cabi.lib()
+    nws = lib.cf_sum_f64_workspace_bytes()
+    if workspace is None:
+        workspace = torch.empty(nws // 8, dtype=torch.float64, device=x.device)
+    with torch.cuda.device(x.device):
+        _cabi.check(lib.cf_sum_f64(x.data_ptr(), x.numel(), out.data_ptr(), workspace.data_ptr(), workspace.numel() * 8,
+                                   _cabi.stream()), "cf_sum_f64")
+    return out
+
+
 # ---------------------------------------------------------------------------------------------------------- lanes
 # Inside one GPU the same independence is worth ~14 % (tools/lanes.py, profiles/r1_lanes_experiment.log): a cine unit of
 # 29 pairs fills the 148 SMs for only ~3 waves per lookup, so every launch pays a latency ramp (coords -> windows -> first

@@ -199,6 +199,13 @@ CF_API int cf_ncc(const float* I, const float* J, int N, int H, int W, int win, 
 CF_API int cf_ncc_bwd(const float* I, const float* J, int N, int H, int W, int win, float eps, const float* grad, int per_pixel,
                float mult, float* grad_I, float* grad_J, void* workspace, size_t ws_bytes, void* stream);
 
+/* Deterministic float64 sum of an fp32 device array (summation order depends on n alone): the compact per-unit results the
+ * cohort driver gathers over NCCL (shard.py; the reference's analysis scripts reduce warped frames / flows to per-frame numbers
+ * the same way, e.g. compute_SSIM.py:89-104) are checked bit for bit against a recomputation.  x must be 16-byte aligned;
+ * workspace of cf_sum_f64_workspace_bytes() bytes; out [1] double. */
+CF_API size_t cf_sum_f64_workspace_bytes(void);
+CF_API int cf_sum_f64(const float* x, size_t n, double* out, void* workspace, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

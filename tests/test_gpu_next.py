@@ -209,3 +209,21 @@ def test_on_the_fly_memory_is_linear_in_hw():
     from cardioflow_b200 import _cabi
     lib = _cabi.lib()
     assert lib.cf_fmap_pyramid_bytes(64, 256, 64, 64, 4) < 0.4e9 < 5.6e9 < lib.cf_corr_pyramid_bytes(64, 64, 64, 4)
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 5, 1023, 592 * 4 + 1, 1 << 20, 9_502_720 + 3])
+def test_sum_f64_is_exact_enough_and_deterministic(n):
+    """cf_sum_f64 (per-unit result rows of the cohort driver): equals the float64 sum of the fp32 values to double rounding,
+    bit-identical across calls, writes only its output slot."""
+    from cardioflow_b200 import shard
+    gen = torch.Generator().manual_seed(n % 1000)
+    x = (torch.randn(n, generator=gen) * 100).cuda()
+    row = torch.full((3,), -7.0, dtype=torch.float64, device="cuda")
+    shard.sum_f64(x, row[1:2])
+    first = row.clone()
+    shard.sum_f64(x, row[1:2])
+    assert torch.equal(first, row) and float(row[0]) == -7.0 and float(row[2]) == -7.0
+    want = x.double().sum()
+    assert abs(float(row[1]) - float(want)) <= 1e-12 * float(x.double().abs().sum()) + 1e-300
+    with pytest.raises(ValueError):
+        shard.sum_f64(x.double(), row[1:2])

@@ -283,7 +283,7 @@ def run_cohort(args, wl):
     lane_pyr = ([torch.empty(lib.cf_corr_pyramid_bytes(b - a, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
                  for a, b in bounds] if len(bounds) > 1 else [pyramid])
     lab = torch.empty(P, 1, IH, IW, dtype=torch.int64, device=dev)
-    lane_counts = torch.zeros(len(bounds), 4, dtype=torch.int64, device=dev)
+    frame_counts = torch.zeros(P, 4, dtype=torch.int64, device=dev)
     sum_ws = torch.empty(lib.cf_sum_f64_workspace_bytes() // 8, dtype=torch.float64, device=dev)
 
     def chain(u, j, a, b):
@@ -292,15 +292,15 @@ def run_cohort(args, wl):
         for k in range(ITERS):
             blk(u["coords"][k, a:b], out=outs[k, a:b])
         cf.warp(u["img"][a:b], u["flow"][a:b], out=warped[a:b])
-        _, cnt = cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4, out=lab[a:b], return_counts=True)
-        lane_counts[j].copy_(cnt.sum(0))                   # per-frame class areas -> the unit's totals
+        cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4, out=lab[a:b], return_counts=True,
+                              counts_out=frame_counts[a:b])   # per-frame class areas, straight into the unit's table
         return blk
 
     def compute(u, row):
         lanes.run(P, lambda j, a, b: chain(u, j, a, b))
         shard.sum_f64(outs[ITERS - 1], row[0:1], sum_ws)     # one pass, fixed summation order (cf_sum_f64)
         shard.sum_f64(warped, row[1:2], sum_ws)
-        row[2:6] = lane_counts.sum(0)                      # warped-label pixel counts (fused into the mask warp)
+        row[2:6] = frame_counts.sum(0)                     # warped-label pixel counts (fused into the mask warp)
 
     with torch.no_grad():
         rows = torch.zeros(max(len(mine), 1), WIDTH, dtype=torch.float64, device=dev)

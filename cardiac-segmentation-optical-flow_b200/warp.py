@@ -63,10 +63,11 @@ def warp(src, flow, mode="bilinear", out=None):
     return _Warp2d.apply(flow, src, _MODES[mode], out)
 
 
-def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False):
+def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False, counts_out=None):
     """argmax_c warp(one_hot(label), flow) without the one-hot intermediate (the `warp_linear` pattern,
     SegFlowGaussian.py:3571-3580).  label [B,1,H,W] integer; returns int64 [B,1,H,W] (written into ``out`` when given).
-    ``return_counts=True`` also returns int64 [B, num_classes]: pixels per class of every warped map, from the same launch."""
+    ``return_counts=True`` also returns int64 [B, num_classes]: pixels per class of every warped map, from the same launch
+    (written into ``counts_out`` when given: e.g. a row slice of a per-cine table that several lanes fill)."""
     if label.dim() != 4 or label.shape[1] != 1 or label.shape[0] != flow.shape[0] or label.shape[2:] != flow.shape[2:]:
         raise ValueError(f"label must be [B, 1, H, W] matching flow {tuple(flow.shape)}, got {tuple(label.shape)}")
     _cabi.require_cuda(flow, label)
@@ -79,7 +80,13 @@ def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False
         raise ValueError("out must be a contiguous int64 tensor of the label's shape on the same device")
     with torch.cuda.device(f.device):
         if return_counts:
-            counts = torch.empty(B, num_classes, dtype=torch.int64, device=lab.device)
+            if counts_out is None:
+                counts = torch.empty(B, num_classes, dtype=torch.int64, device=lab.device)
+            else:
+                counts = counts_out
+                if (counts.dtype != torch.int64 or tuple(counts.shape) != (B, num_classes) or not counts.is_contiguous()
+                        or counts.device != lab.device):
+                    raise ValueError(f"counts_out must be a contiguous int64 [{B}, {num_classes}] tensor on the label's device")
             _cabi.check(_cabi.lib().cf_warp2d_onehot_argmax_counts(f.data_ptr(), lab.data_ptr(), num_classes, B, H, W,
                                                                    out.data_ptr(), counts.data_ptr(), _cabi.stream()),
                         "cf_warp2d_onehot_argmax_counts")

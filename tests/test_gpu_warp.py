@@ -110,6 +110,13 @@ def test_onehot_argmax_counts(shape, ncls):
     # counts are overwritten, not accumulated, by a second call into the same storage
     out2, counts2 = cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, return_counts=True)
     assert torch.equal(counts2, counts)
+    # counts_out: a row slice of a larger table is filled in place, rows outside it stay untouched
+    table = torch.full((B + 2, ncls), -1, dtype=torch.int64, device=DEV)
+    _, c3 = cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, return_counts=True, counts_out=table[1:B + 1])
+    assert c3.data_ptr() == table[1:].data_ptr() and torch.equal(table[1:B + 1], counts)
+    assert bool((table[0] == -1).all()) and bool((table[B + 1] == -1).all())
+    with pytest.raises(ValueError):
+        cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, return_counts=True, counts_out=table)
     with pytest.raises(ValueError):
         cf.warp_onehot_argmax(flow.to(DEV), label.to(DEV), ncls, out=torch.empty(B, 1, H, W, device=DEV))
 

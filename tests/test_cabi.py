@@ -123,3 +123,24 @@ int main(void) {
     assert r.returncode == 0, r.stderr
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0 and "c host ok" in r.stdout, (r.returncode, r.stdout, r.stderr)
+
+
+def test_ncc_host_contract_without_a_gpu():
+    """cardioflow_b200.NCC keeps the constructor / input contract of nnunet/lib/loss.py:15-76 and has no CPU path."""
+    a = torch.rand(2, 1, 16, 16)
+    loss = cf.NCC()
+    assert (loss.win, loss.eps, loss.reduction) == (9, 1e-3, "mean") and len(list(loss.parameters())) == 0
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        loss(a, a)
+    with pytest.raises(ValueError, match="5-D"):
+        cf.NCC(reduction=None)(a, a)
+    with pytest.raises(ValueError, match="single-channel"):
+        loss(torch.rand(2, 3, 16, 16), torch.rand(2, 3, 16, 16))
+    with pytest.raises(ValueError, match="differ"):
+        loss(a, torch.rand(2, 1, 16, 17))
+    lib = _cabi.lib()
+    assert lib.cf_ncc(None, None, 1, 8, 8, 9, 1e-3, None, None, None, 0, None) == _cabi.CF_ERR_BAD_ARG
+    assert lib.cf_ncc(ctypes.c_void_p(256), ctypes.c_void_p(512), 1, 8, 8, 7, 1e-3, ctypes.c_void_p(1024), None, None, 0, None) \
+        == _cabi.CF_ERR_UNSUPPORTED and b"win 7" in lib.cf_last_error()
+    assert lib.cf_ncc_workspace_bytes(300, 224, 224, 0) % 256 == 0 and lib.cf_ncc_workspace_bytes(0, 8, 8, 1) == 0
+    assert lib.cf_sum_f64(None, 4, None, None, 0, None) == _cabi.CF_ERR_BAD_ARG and lib.cf_sum_f64_workspace_bytes() >= 8

@@ -300,7 +300,7 @@ def run_cohort(args, wl):
         lanes.run(P, lambda j, a, b: chain(u, j, a, b))
         shard.sum_f64(outs[ITERS - 1], row[0:1], sum_ws)     # one pass, fixed summation order (cf_sum_f64)
         shard.sum_f64(warped, row[1:2], sum_ws)
-        row[2:6] = frame_counts.sum(0)                     # warped-label pixel counts (fused into the mask warp)
+        torch.sum(frame_counts, dim=0, dtype=torch.float64, out=row[2:6])   # warped-label pixel counts (from the mask warp launch)
 
     with torch.no_grad():
         rows = torch.zeros(max(len(mine), 1), WIDTH, dtype=torch.float64, device=dev)
@@ -340,6 +340,12 @@ def run_cohort(args, wl):
         sampler = ClockSampler(local_rank)
         sampler.start()
         evs = [run_unit(shard.unit_seed(pat, sl), rows[i]) for i, (pat, sl) in enumerate(mine)]
+        # The per-unit intervals exclude the (untimed) input synthesis between units, whose wall-clock cost differs from rank
+        # to rank; without a barrier here that skew would be charged to the gather as waiting time.  Compute skew is already
+        # in the max over ranks of compute_ms; the gather is timed from a common start.
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         g0.record()
         table = shard.gather_results(rows[:len(mine)], len(units), rank=rank, world_size=world)
@@ -355,10 +361,11 @@ def run_cohort(args, wl):
                 run_unit(shard.unit_seed(*units[j]), scratch)
                 check.append(bool(torch.equal(scratch, table[j])))
             torch.cuda.synchronize()
-    t = torch.tensor([compute_ms + gather_ms, compute_ms, gather_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([compute_ms, gather_ms], dtype=torch.float64, device=dev)
     if dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, compute_ms, gather_ms = t.tolist()
+    compute_ms, gather_ms = t.tolist()
+    total_ms = compute_ms + gather_ms            # slowest rank's compute, then the gather from the common barrier
     if rank == 0:
         n_pairs = len(units) * P
         line = {
@@ -371,6 +378,7 @@ def run_cohort(args, wl):
                        "launch": "eager launches from Python, one unit at a time" if args.no_graph else "one CUDA graph replay per unit (build + 12 lookups + warp + mask warp + result row)",
                        "l2": "every unit has fresh inputs and writes 623 MB (> 126 MB L2)"},
             "clocks": clocks, "compute_ms_max_rank": compute_ms, "gather_ms_max_rank": gather_ms,
+            "timing": "value = pairs / (max over ranks of the summed per-unit device intervals + max over ranks of the gather timed from a barrier)",
             "gather": {"collective": "all_gather_into_tensor (NCCL)" if world > 1 else "none (1 rank)",
                        "bytes_per_rank": int(rows[:len(mine)].numel() * 8), "rows_verified_on_rank0": check},
             "gpu_launches": len(mine) * ((2 + ITERS + 2) * len(bounds) + 4),   # + two cf_sum_f64 (2 launches each)

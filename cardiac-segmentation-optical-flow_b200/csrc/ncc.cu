@@ -34,6 +34,9 @@ constexpr int kInCols = 128, kOutCols = kInCols - 2 * kHalo;   // 120 output col
 #ifndef NCC_MINB
 #define NCC_MINB 1
 #endif
+#ifndef NCC_PF
+#define NCC_PF 1   // rows of look-ahead in the walk (1 or 2)
+#endif
 constexpr int kRows = NCC_ROWS;                                // output rows per task (+9 priming rows of adds only)
 constexpr int kWarps = 1;   // one warp per CTA: the task is a function of blockIdx alone, so the compiler sees the row loop as
                             // warp-uniform and emits plain SHFLs (with 4 warps per CTA every shuffle carried a divergence check)
@@ -159,11 +162,23 @@ __device__ __forceinline__ void box5_walk(const Task& k, int W, const Load& load
     // rows y0-5 .. y0+3: the window of output row y0 - 1 (row y0-5 leaves in the first iteration)
 #pragma unroll 3
     for (int j = -kHalo - 1; j < kHalo; ++j) load.accumulate(V, load.fetch(k.y0 + j), 1.0f);
+#if NCC_PF == 2
+    // rows fetched two iterations ahead of their use (Load::kDeep loaders only: the pair loader's rows are 8 registers each)
+    typename Load::Raw enter = load.fetch(k.y0 + kHalo), leave = load.fetch(k.y0 - kHalo - 1);
+    typename Load::Raw enter2 = load.fetch(k.y0 + kHalo + 1), leave2 = load.fetch(k.y0 - kHalo);
+    for (int y = k.y0; y < k.y0 + k.rows; ++y) {
+        const typename Load::Raw e = enter, l = leave;
+        enter = enter2;
+        leave = leave2;
+        enter2 = load.fetch(y + 2 + kHalo);
+        leave2 = load.fetch(y + 1 - kHalo);
+#else
     typename Load::Raw enter = load.fetch(k.y0 + kHalo), leave = load.fetch(k.y0 - kHalo - 1);
     for (int y = k.y0; y < k.y0 + k.rows; ++y) {
         const typename Load::Raw e = enter, l = leave;
         enter = load.fetch(y + 1 + kHalo);        // next iteration's rows: in flight while this row is computed
         leave = load.fetch(y - kHalo);
+#endif
         load.accumulate(V, e, 1.0f);
         load.accumulate(V, l, -1.0f);
         QN<NQ> S;

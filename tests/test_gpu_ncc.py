@@ -173,3 +173,28 @@ def test_outputs_stay_inside_their_buffers(shape):
                                    ws.data_ptr(), 5 * npx * 4, _cabi.stream()))
         torch.cuda.synchronize()
         assert intact(wbuf, 5 * npx) and intact(ibuf, npx) and intact(jbuf, npx)
+
+
+def test_forward_is_capturable_in_a_cuda_graph():
+    """cf_ncc only enqueues on the current stream (no hidden synchronisation): a captured forward replays on new data."""
+    import cardioflow_b200 as cf
+    gen = torch.Generator().manual_seed(3)
+    I, J = torch.rand(3, 1, 64, 72, generator=gen).cuda(), torch.rand(3, 1, 64, 72, generator=gen).cuda()
+    loss_fn = cf.NCC()
+    with torch.no_grad():
+        eager = loss_fn(I, J).clone()
+        torch.cuda.synchronize()
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            loss_fn(I, J)                                   # warm the allocator on the capture stream
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            out = loss_fn(I, J)
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, eager)
+        I.copy_(torch.rand(3, 1, 64, 72, generator=gen))    # new data in the captured buffers
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, loss_fn(I, J)) and not torch.equal(out, eager)

@@ -279,3 +279,45 @@ def test_lanes_are_bit_identical_to_one_chain(n_lanes, graph):
         torch.cuda.synchronize()
     assert len(keep) == n_lanes
     assert torch.equal(out_o, ref_o) and torch.equal(out_w, ref_w)
+
+
+def test_full_batch_cfg2_production_path():
+    """BASELINE cfg 2 exactly as bench.py runs it: 29 pairs, 256 channels, 32x32 fmaps, bf16 tensor-core build (level 0 stored
+    as 4x4 tiles), two lanes.  (1) every lane's lookups are BIT-EXACT against the C oracle run on the pyramid the GPU built
+    (the lookup adds no error of its own at full batch); (2) the pyramid is within the stated 1e-2 of the fp32 oracle;
+    (3) pooling levels equal avg_pool2d of the level below, bit for bit."""
+    b, c, h, w = 29, 256, 32, 32
+    g = torch.Generator().manual_seed(1002)
+    base = torch.randn(c, h, w, generator=g)
+    frames = [base]
+    for t in range(b):
+        frames.append(torch.roll(frames[-1], shifts=(t % 3 - 1, 1), dims=(1, 2)) + 0.1 * torch.randn(c, h, w, generator=g))
+    frames = torch.stack(frames)
+    f1, f2 = frames[:-1].contiguous(), frames[1:].contiguous()
+    grid = corr_oracle.coords_grid(b, h, w)
+    traj = [grid, grid + torch.randn(b, 2, h, w, generator=g) * 1.2, grid + torch.randn(b, 2, h, w, generator=g) * 1.7]
+    f1d, f2d = f1.to(DEV), f2.to(DEV)
+    outs = [torch.empty(b, 324, h, w, device=DEV) for _ in traj]
+    lanes = cf.Lanes(2, DEV)
+    blocks = {}
+
+    def chain(j, lo, hi):
+        blk = cf.CorrBlock(f1d[lo:hi], f2d[lo:hi], num_levels=4, radius=4, precision="bf16")
+        for k, co in enumerate(traj):
+            blk(co[lo:hi].to(DEV), out=outs[k][lo:hi])
+        blocks[j] = (lo, hi, blk)
+    with torch.no_grad():
+        lanes.run(b, chain)
+    torch.cuda.synchronize()
+    ref = corr_oracle.CorrBlock(f1, f2)                                        # fp32 CPU oracle, whole batch
+    for lo, hi, blk in blocks.values():
+        pyr = [p.cpu() for p in blk.corr_pyramid]                              # un-tiled views of what the GPU built
+        for l in range(4):
+            want = ref.corr_pyramid[l].view(b, h * w, *ref.corr_pyramid[l].shape[1:])[lo:hi].reshape(pyr[l].shape)
+            assert rel_err(pyr[l].numpy(), want.numpy()) <= 1e-2, l
+            if l:
+                assert torch.equal(pyr[l], torch.nn.functional.avg_pool2d(pyr[l - 1], 2, stride=2)), l
+        for k, co in enumerate(traj):
+            want_c = c_oracle.lookup([p.numpy() for p in pyr], co[lo:hi].contiguous().numpy())
+            assert np.array_equal(outs[k][lo:hi].cpu().numpy(), want_c), (lo, hi, k)
+    assert rel_err(outs[2].cpu().numpy(), ref(traj[2]).numpy()) <= 1e-2

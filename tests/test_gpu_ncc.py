@@ -198,3 +198,25 @@ def test_forward_is_capturable_in_a_cuda_graph():
         g.replay()
         torch.cuda.synchronize()
         assert torch.equal(out, loss_fn(I, J)) and not torch.equal(out, eager)
+
+
+def test_full_size_properties_cfg3_batch():
+    """300 x 224^2 (the BASELINE cfg 3 batch, the frames the warp produces): size-independent properties of the loss."""
+    import cardioflow_b200 as cf
+    g = torch.Generator(device="cuda").manual_seed(1003)
+    n, h, w = 300, 224, 224
+    I = torch.rand(n, 1, h, w, device="cuda", generator=g)
+    J = (I + 0.1 * torch.randn(n, 1, h, w, device="cuda", generator=g)).contiguous()
+    with torch.no_grad():
+        ncc = cf.NCC()
+        lij, lji = ncc(I, J), ncc(J, I)
+        assert abs(float(lij) - float(lji)) <= 1e-6                              # symmetric in its arguments
+        assert abs(float(ncc(2.5 * I + 0.0, J)) - float(lij)) <= 2e-4           # cc is invariant to gain up to the eps term
+        m = cf.NCC(reduction=None)(I[None], J[None])                             # [1, n, 1, h, w]
+        assert m.shape == (1, n, 1, h, w) and float(m.min()) >= 0.001 - 1e-7 and float(m.max()) <= 0.999 + 1e-7
+        assert abs(float(m.double().mean()) - float(lij)) <= 1e-6               # the mean path equals the mean of the map
+        parts = torch.stack([ncc(I[k:k + 60], J[k:k + 60]) for k in range(0, n, 60)])
+        assert abs(float(parts.double().mean()) - float(lij)) <= 1e-6           # images are independent: batch splits agree
+        same = ncc(I, I)
+        assert float(same) < float(lij) and float(same) < 0.05                   # identical images: cc ~ var^2 / (var^2 + eps)
+        assert torch.equal(ncc(I, J), lij)                                       # deterministic reduction

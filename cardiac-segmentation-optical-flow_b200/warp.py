@@ -22,6 +22,11 @@ class _Warp2d(torch.autograd.Function):
             out = torch.empty_like(src)
         elif out.shape != src.shape or out.dtype != torch.float32 or not out.is_contiguous():
             raise ValueError(f"out must be a contiguous fp32 tensor of shape {tuple(src.shape)}")
+        ctx.empty = src.numel() == 0          # empty batch / zero channels: grid_sample returns an empty tensor, so do we
+        if ctx.empty:
+            ctx.save_for_backward(f, src)
+            ctx.mode = mode
+            return out
         with torch.cuda.device(src.device):
             _cabi.check(_cabi.lib().cf_warp2d(f.data_ptr(), src.data_ptr(), B, C, H, W, mode, out.data_ptr(),
                                               _cabi.stream()), "cf_warp2d")
@@ -39,6 +44,8 @@ class _Warp2d(torch.autograd.Function):
         need_flow, need_src = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         gsrc = torch.zeros_like(src) if need_src else None
         gflow = torch.empty_like(f) if need_flow else None
+        if ctx.empty:
+            return (gflow.zero_() if need_flow else None), gsrc, None, None
         with torch.cuda.device(src.device):
             _cabi.check(_cabi.lib().cf_warp2d_bwd(f.data_ptr(), src.data_ptr(), go.data_ptr(), B, C, H, W,
                                                   gsrc.data_ptr() if need_src else None,
@@ -78,6 +85,10 @@ def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False
         out = torch.empty_like(lab)
     elif out.dtype != torch.int64 or out.shape != lab.shape or not out.is_contiguous() or out.device != lab.device:
         raise ValueError("out must be a contiguous int64 tensor of the label's shape on the same device")
+    if lab.numel() == 0:                      # empty batch: nothing to warp (argmax of an empty one-hot stack is empty)
+        if return_counts:
+            return out, (counts_out if counts_out is not None else torch.zeros(B, num_classes, dtype=torch.int64, device=lab.device))
+        return out
     with torch.cuda.device(f.device):
         if return_counts:
             if counts_out is None:

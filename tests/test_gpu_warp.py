@@ -179,3 +179,20 @@ def test_utils_warp_backward_matches_autograd_of_the_oracle(shape):
     cf.utils_warp(xg, fg).backward(gout.cuda())
     assert rel_err(xg.grad.cpu().numpy(), xr.grad.numpy()) <= 1e-5
     assert rel_err(fg.grad.cpu().numpy(), fr.grad.numpy()) <= 1e-4
+
+
+def test_empty_batch_and_zero_channels_return_empty_like_grid_sample():
+    """Edge case the ATen path of the reference accepts: B = 0 or C = 0 give empty outputs (and gradients), no kernel launch."""
+    st = cf.SpatialTransformer((16, 20)).to(DEV)
+    out = st(torch.zeros(0, 2, 16, 20, device=DEV), torch.zeros(0, 3, 16, 20, device=DEV))
+    assert out.shape == (0, 3, 16, 20)
+    flow = torch.zeros(2, 2, 16, 20, device=DEV, requires_grad=True)
+    out = st(flow, torch.zeros(2, 0, 16, 20, device=DEV))
+    assert out.shape == (2, 0, 16, 20)
+    out.sum().backward()
+    assert flow.grad is not None and not bool(flow.grad.any())
+    lab, cnt = cf.warp_onehot_argmax(torch.zeros(0, 2, 16, 20, device=DEV), torch.zeros(0, 1, 16, 20, dtype=torch.int64, device=DEV),
+                                     return_counts=True)
+    assert lab.shape == (0, 1, 16, 20) and cnt.shape == (0, 4)
+    want = warp_oracle.SpatialTransformer((16, 20))(torch.zeros(0, 2, 16, 20), torch.zeros(0, 3, 16, 20))
+    assert want.shape == out.new_zeros(0, 3, 16, 20).shape

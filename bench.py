@@ -13,7 +13,8 @@ Prints ONE JSON line (rank 0).  `value` = device-resident throughput; `e2e` = th
 public module API with pinned HOST buffers (H2D of every input + D2H of every output inside the timed
 region); `roofline` = the dominant kernel (the lookup) against the measured HBM peak; `cpu_baseline` = the
 oracle (torch CPU kernels, the ATen ops the reference's Python dispatches to) on a bounded sample.
-`--impl reference` times that CPU implementation alone (the reference arm).
+`--impl reference` times that CPU implementation alone (the reference arm).  `--impl reference-gpu` (informational, cfg2 / cfg4)
+times the same oracle with torch CUDA ops on one B200: the reference "as actually run" (SURVEY.md 8(d)).
 """
 import argparse
 import json
@@ -223,6 +224,72 @@ def run_reference_arm(args, wl):
         "gpu_launches": 0,
     }
     emit(line)
+
+
+
+def run_reference_gpu(args, wl):
+    """SURVEY.md 8(d) / BASELINE.md section 4 "reference as actually run": the same oracle (the ATen ops the reference's Python
+    dispatches to: matmul, avg_pool2d, grid_sample, cat/permute) executed with torch CUDA kernels on one B200, device-resident
+    inputs, CUDA-event timing.  Informational "before" for the hand-written kernels; not the driver's reference arm (that is the
+    CPU path, --impl reference).  Two figures: the reference's own loop structure (one CorrBlock per pair, SegFlowGaussian.py:907-954)
+    and the best case for ATen (all pairs of the step in one batched CorrBlock)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if not torch.cuda.is_available():
+        sys.exit("--impl reference-gpu needs a CUDA device")
+    from oracle import corr_oracle, warp_oracle
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    P = wl["pairs"]
+    unit = make_unit(wl, seed=1002, device=dev)
+    st = warp_oracle.SpatialTransformer((wl["IH"], wl["IW"])).to(dev)
+
+    def per_pair():
+        for p in range(P):
+            blk = corr_oracle.CorrBlock(unit["f1"][p:p + 1], unit["f2"][p:p + 1], num_levels=LEVELS, radius=RADIUS)
+            for k in range(ITERS):
+                blk(unit["coords"][k, p:p + 1])
+            st(flow=unit["flow"][p:p + 1], original=unit["img"][p:p + 1])
+
+    def batched():
+        blk = corr_oracle.CorrBlock(unit["f1"], unit["f2"], num_levels=LEVELS, radius=RADIUS)
+        for k in range(ITERS):
+            blk(unit["coords"][k])
+        st(flow=unit["flow"], original=unit["img"])
+
+    def timed(fn, steps):
+        for _ in range(max(args.warmup, 1)):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    with torch.no_grad():
+        steps = max(1, min(args.steps, 20))
+        ms_pair = timed(per_pair, steps)
+        batch_note = ""
+        try:
+            ms_batch = timed(batched, steps)
+        except RuntimeError as e:          # cuDNN's grid_sample refuses very large N (cfg4: 262 144 "images"): native ATen kernel
+            torch.cuda.synchronize()
+            batch_note = " [cuDNN grid_sample refused this batch (%s); timed with torch.backends.cudnn disabled]" % str(e).split(".")[0]
+            with torch.backends.cudnn.flags(enabled=False):
+                ms_batch = timed(batched, steps)
+    emit({"impl": "reference-gpu", "metric": METRIC, "value": P / (ms_pair * 1e-3), "unit": "frame-pairs/s", "n_gpus": 1,
+          "steps": steps, "warmup": max(args.warmup, 1), "ms_per_step": ms_pair, "higher_is_better": True, "scaling": "weak",
+          "vs_baseline": None, "dtype": "f32 (ATen CUDA: matmul may use TF32 only if the user enables it; defaults kept)",
+          "data": "synthetic",
+          "config": {"workload": args.workload + ": " + wl["desc"],
+                     "what": "torch CUDA eager ops of the oracle (matmul, /sqrt(C), 3 x avg_pool2d, per level grid_sample + cat + "
+                             "permute), one CorrBlock per pair as the reference loops; device-resident inputs"},
+          "batched": {"value": P / (ms_batch * 1e-3), "ms_per_step": ms_batch,
+                      "what": "all pairs of the step in ONE batched CorrBlock / lookup / warp call (best case for ATen)" + batch_note},
+          "gpu_launches": 0})
 
 
 # ------------------------------------------------------------------------------------------------ cfg5 cohort
@@ -501,7 +568,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp32"])
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying one CUDA graph per step")
@@ -520,6 +587,10 @@ def main():
 
     if args.impl == "reference":
         return run_reference_arm(args, wl)
+    if args.impl == "reference-gpu":
+        if args.workload not in ("cfg2", "cfg4"):
+            sys.exit("--impl reference-gpu covers cfg2 and cfg4")
+        return run_reference_gpu(args, wl)
     if args.workload == "cfg5":
         return run_cohort(args, wl)
     if args.workload == "cfg3":

@@ -42,6 +42,8 @@ def emit(line):
 
 WORKLOADS = {
     # name: pairs, C, fmap H, W, image H, W
+    "cfg1": dict(pairs=1, C=256, H=28, W=28, IH=224, IW=224,
+                 desc="configs[0]: single frame pair, 256-ch fmaps 28x28 (224^2 input), 4 levels, r=4, 12 lookups, one 224^2 warp"),
     "cfg2": dict(pairs=29, C=256, H=32, W=32, IH=256, IW=256,
                  desc="configs[1]: 29 frame pairs, 256-ch fmaps 32x32 (256^2 input), 4 levels, r=4, 12 lookups, 29 warps"),
     "cfg5": dict(pairs=29, C=256, H=32, W=32, IH=256, IW=256,
@@ -169,8 +171,8 @@ def run_reference_arm(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = 1 if args.workload == "cfg4" else 4
-    threads = os.cpu_count() or 1
+    sample = 1 if args.workload in ("cfg4", "cfg1") else 4
+    threads = args.cpu_threads or os.cpu_count() or 1
     torch.set_num_threads(threads)
     from oracle import corr_oracle, warp_oracle
     if args.workload == "cfg3":          # the warp alone: 30 of the 300 five-channel frames per step
@@ -574,6 +576,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying one CUDA graph per step")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-threads", type=int, default=0, help="--impl reference: host threads (default: all; 1 = per-core figure)")
     ap.add_argument("--l2-persist-mb", type=int, default=0,
                     help="experiment: cudaLimitPersistingL2CacheSize in MB (the lookup's pyramid reads carry L2 evict_last hints)")
     ap.add_argument("--lanes", type=int, default=2,
@@ -588,8 +591,8 @@ def main():
     if args.impl == "reference":
         return run_reference_arm(args, wl)
     if args.impl == "reference-gpu":
-        if args.workload not in ("cfg2", "cfg4"):
-            sys.exit("--impl reference-gpu covers cfg2 and cfg4")
+        if args.workload not in ("cfg1", "cfg2", "cfg4"):
+            sys.exit("--impl reference-gpu covers cfg1, cfg2 and cfg4")
         return run_reference_gpu(args, wl)
     if args.workload == "cfg5":
         return run_cohort(args, wl)

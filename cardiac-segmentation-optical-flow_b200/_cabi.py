@@ -40,11 +40,13 @@ _SIGNATURES = {
     "cf_warp2d_onehot_argmax": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "cf_warp2d_onehot_argmax_counts": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_warp2d_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_warp2d_nearest_bwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "cf_corr_lookup_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "cf_corr_pool_bwd": (_I, [_P, _I, _I, _I, _I, _P]),
     "cf_corr_volume_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_vecint": (_I, [_P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_sample_points": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_sample_points_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "cf_warp2d_xy": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "cf_warp2d_xy_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_upsample_convex": (_I, [_P, _P, _I, _I, _I, _I, _I, _c.c_float, _P, _P]),

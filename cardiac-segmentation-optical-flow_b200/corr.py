@@ -56,7 +56,7 @@ class _CorrBuild(torch.autograd.Function):
     """(fmap1, fmap2) -> packed pyramid.  a2 + a3 of SURVEY.md 8(a)."""
 
     @staticmethod
-    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None, allow_tiled=False, info=None):
+    def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None, allow_tiled=False, info=None, gstate=None):
         B, C, H, W = fmap1.shape
         lib = _cabi.lib()
         f1, f2 = _cabi.f32c(fmap1), _cabi.f32c(fmap2)
@@ -82,6 +82,7 @@ class _CorrBuild(torch.autograd.Function):
         ctx.save_for_backward(f1, f2)
         ctx.meta = (B, C, H, W, num_levels)
         ctx.used_precision = used.value
+        ctx.gstate = gstate
         return pyramid
 
     @staticmethod
@@ -89,14 +90,18 @@ class _CorrBuild(torch.autograd.Function):
         f1, f2 = ctx.saved_tensors
         B, C, H, W, L = ctx.meta
         lib = _cabi.lib()
-        g = grad_pyramid.contiguous().clone()
+        shared = ctx.gstate.pop("buf", None) if ctx.gstate is not None else None
+        if shared is not None and grad_pyramid.data_ptr() == shared.data_ptr():
+            g = shared                          # the lookups' own accumulation buffer: pooled in place, no copy
+        else:
+            g = grad_pyramid.contiguous().clone()
         gf1, gf2 = torch.empty_like(f1), torch.empty_like(f2)
         with torch.cuda.device(f1.device):
             s = _cabi.stream()
             _cabi.check(lib.cf_corr_pool_bwd(g.data_ptr(), B, H, W, L, s), "cf_corr_pool_bwd")
             _cabi.check(lib.cf_corr_volume_bwd(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W,
                                                gf1.data_ptr(), gf2.data_ptr(), s), "cf_corr_volume_bwd")
-        return gf1, gf2, None, None, None, None, None
+        return gf1, gf2, None, None, None, None, None, None
 
 
 class _CorrLookup(torch.autograd.Function):
@@ -104,7 +109,7 @@ class _CorrLookup(torch.autograd.Function):
     (the reference detaches them before every lookup, SegFlowGaussian.py:933)."""
 
     @staticmethod
-    def forward(ctx, pyramid, coords, meta, out=None, tiled_mask=0):
+    def forward(ctx, pyramid, coords, meta, out=None, tiled_mask=0, gstate=None):
         B, H, W, L, r = meta
         c = _cabi.f32c(coords)
         shape = (B, L * (2 * r + 1) ** 2, H, W)
@@ -118,18 +123,30 @@ class _CorrLookup(torch.autograd.Function):
         ctx.save_for_backward(c)
         ctx.meta = meta
         ctx.numel = pyramid.numel()
+        ctx.gstate = gstate
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
         (c,) = ctx.saved_tensors
         B, H, W, L, r = ctx.meta
-        g = torch.zeros(ctx.numel, dtype=torch.float32, device=grad_out.device)
+        # The 12 lookups of one CorrBlock add their gradients into ONE zeroed pyramid-sized buffer (the kernel accumulates).
+        # The first backward of a pass hands that buffer to autograd as the pyramid's gradient, the others return None; the
+        # build's backward runs after all of them (it depends on every lookup node) and takes the buffer out of `gstate`.
+        # A buffer left over from another backward pass (e.g. gradients taken w.r.t. the pyramid itself) is never reused.
+        task = torch._C._current_graph_task_id()
+        first = ctx.gstate is None or ctx.gstate.get("buf") is None or ctx.gstate.get("task") != task
+        if first:
+            g = torch.zeros(ctx.numel, dtype=torch.float32, device=grad_out.device)
+            if ctx.gstate is not None:
+                ctx.gstate["buf"], ctx.gstate["task"] = g, task
+        else:
+            g = ctx.gstate["buf"]
         go = grad_out.contiguous().float()
         with torch.cuda.device(go.device):
             _cabi.check(_cabi.lib().cf_corr_lookup_bwd(c.data_ptr(), go.data_ptr(), B, H, W, L, r, g.data_ptr(),
                                                        _cabi.stream()), "cf_corr_lookup_bwd")
-        return g, None, None, None, None
+        return (g if first else None), None, None, None, None, None
 
 
 class CorrBlock:
@@ -182,7 +199,9 @@ class CorrBlock:
         needs_grad = torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)
         allow_tiled = not needs_grad and os.environ.get("CARDIOFLOW_TILED", "1") != "0"
         info = {}
-        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer, allow_tiled, info)
+        self._gstate = {}      # gradient pyramid shared by the backward passes of this block's lookups
+        self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer, allow_tiled, info,
+                                         self._gstate)
         self.used_precision = {0: "bf16", 1: "fp32"}.get(info.get("used_precision", -1), "?")
         self._tiled_mask = info.get("tiled_mask", 0)
         self._views = None
@@ -235,7 +254,7 @@ class CorrBlock:
         if self.on_the_fly:
             return self._lookup_on_the_fly(coords, out)
         _cabi.require_cuda(self._pyramid, coords)
-        return _CorrLookup.apply(self._pyramid, coords, self._meta, out, self._tiled_mask)
+        return _CorrLookup.apply(self._pyramid, coords, self._meta, out, self._tiled_mask, getattr(self, "_gstate", None))
 
     def _lookup_on_the_fly(self, coords, out=None):
         B, H, W, L, r = self._meta

@@ -4,7 +4,8 @@
 //
 //   cf_corr_lookup_bwd   d(lookup)/d(pyramid): every (query, level) owns a private h_l x w_l image, so the 81
 //                        bilinear taps of a query scatter into a window that NO other thread touches -> the
-//                        window is accumulated in shared memory and written with plain stores (no atomics).
+//                        window is accumulated in shared memory and ADDED to the gradient pyramid with plain
+//                        read-modify-writes (no atomics): the lookups of one CorrBlock share one gradient buffer.
 //                        No gradient w.r.t. coords: the reference detaches them (SegFlowGaussian.py:933).
 //   cf_corr_pool_bwd     backward of the avg_pool2d chain, coarse -> fine, in place: g_l += up2(g_{l+1}) / 4.
 //   cf_corr_volume_bwd   d(corr)/d(fmaps): gf1 = f2 . G^T / sqrt(C), gf2 = f1 . G / sqrt(C) with G = grad of
@@ -103,7 +104,9 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
         for (int c = lane; c < CELLS; c += 32) {
             const int wy = c / PR, wx = c - wy * PR;
             const int y = qy + wy, x = qx + wx;
-            if ((unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl) img[(size_t)y * wl + x] = src[c];
+            // accumulate: the 12 lookups of one CorrBlock add into ONE gradient pyramid (launches are stream-ordered and a
+            // (query, level) image belongs to one warp, so a plain read-modify-write is race-free)
+            if ((unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl) img[(size_t)y * wl + x] += src[c];
         }
     }
 }

@@ -53,13 +53,16 @@ int check_corr_shape(int B, int H, int W, int L, LevelDims* d) {
 
 using namespace cf;
 
+#ifdef CF_BRINGUP
 namespace cf { void corr_tcgen05_set_debug(float* p); void corr_tcgen05_set_timestamps(unsigned long long* p, int cta); }
+#endif
 
 extern "C" {
 
-// bring-up hook, not part of the public header
+#ifdef CF_BRINGUP   // bring-up hooks (CF_NVCC_EXTRA=-DCF_BRINGUP): not in the public header, not in the shipped library
 CF_API void cf_debug_set_gemm_dump(float* p) { cf::corr_tcgen05_set_debug(p); }
 CF_API void cf_debug_set_gemm_timestamps(unsigned long long* p, int cta) { cf::corr_tcgen05_set_timestamps(p, cta); }
+#endif
 
 int cf_version(void) { return 100; }
 
@@ -245,6 +248,12 @@ int cf_warp2d_bwd(const float* flow, const float* src, const float* grad_out, in
     return launch_warp2d_bwd(flow, src, grad_out, B, C, H, W, grad_src, grad_flow, (cudaStream_t)stream);
 }
 
+int cf_warp2d_nearest_bwd(const float* flow, const float* grad_out, int B, int C, int H, int W, float* grad_src, void* stream) {
+    CF_REQUIRE(flow && grad_out && grad_src, CF_ERR_BAD_ARG, "cf_warp2d_nearest_bwd: null pointer");
+    CF_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_warp2d_nearest_bwd: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    return launch_warp2d_nearest_bwd(flow, grad_out, B, C, H, W, grad_src, (cudaStream_t)stream);
+}
+
 int cf_corr_lookup_bwd(const float* coords, const float* grad_out, int B, int H, int W, int L, int r,
                        float* grad_pyramid, void* stream) {
     CF_REQUIRE(coords && grad_out && grad_pyramid, CF_ERR_BAD_ARG, "cf_corr_lookup_bwd: null pointer");
@@ -286,6 +295,16 @@ int cf_sample_points(const float* locs, const float* src, int B, int C, int H, i
     CF_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1 && P > 0 && size_h > 1 && size_w > 1, CF_ERR_BAD_ARG, "cf_sample_points: bad shape");
     CF_REQUIRE(mode == CF_MODE_BILINEAR || mode == CF_MODE_NEAREST, CF_ERR_UNSUPPORTED, "cf_sample_points: mode %d", mode);
     return launch_sample_points(locs, src, B, C, H, W, P, size_h, size_w, mode, out, (cudaStream_t)stream);
+}
+
+int cf_sample_points_bwd(const float* locs, const float* src, const float* grad_out, int B, int C, int H, int W, int P,
+                         int size_h, int size_w, int mode, float* grad_src, float* grad_locs, void* stream) {
+    CF_REQUIRE(locs && src && grad_out, CF_ERR_BAD_ARG, "cf_sample_points_bwd: null pointer");
+    CF_REQUIRE(grad_src || grad_locs, CF_ERR_BAD_ARG, "cf_sample_points_bwd: neither grad_src nor grad_locs requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1 && P > 0 && size_h > 1 && size_w > 1, CF_ERR_BAD_ARG, "cf_sample_points_bwd: bad shape");
+    CF_REQUIRE(mode == CF_MODE_BILINEAR || mode == CF_MODE_NEAREST, CF_ERR_UNSUPPORTED, "cf_sample_points_bwd: mode %d", mode);
+    return launch_sample_points_bwd(locs, src, grad_out, B, C, H, W, P, size_h, size_w, mode, grad_src, grad_locs,
+                                    (cudaStream_t)stream);
 }
 
 int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, void* stream) {

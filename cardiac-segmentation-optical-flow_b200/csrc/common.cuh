@@ -90,9 +90,12 @@ int launch_warp2d_onehot_argmax(const float* flow, const int64_t* label, int ncl
                                 int64_t* out, int64_t* counts, cudaStream_t s);   // counts: nullptr or [B, ncls]
 int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W,
                       float* gsrc, float* gflow, cudaStream_t s);
+int launch_warp2d_nearest_bwd(const float* flow, const float* go, int B, int C, int H, int W, float* gsrc, cudaStream_t s);
 int launch_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, cudaStream_t s);
 int launch_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int SH, int SW,
                          int mode, float* out, cudaStream_t s);
+int launch_sample_points_bwd(const float* locs, const float* src, const float* go, int B, int C, int H, int W, int P, int SH,
+                             int SW, int mode, float* gsrc, float* glocs, cudaStream_t s);
 
 int launch_pool2x2(const float* in, float* out, long n_img, int h, int w, cudaStream_t s);
 int launch_pool_chain(float* pyramid, const LevelDims& d, long n_img, int L, int from_level, cudaStream_t s,

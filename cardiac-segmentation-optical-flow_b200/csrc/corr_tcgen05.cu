@@ -69,7 +69,11 @@ __device__ __forceinline__ unsigned long long gtime() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
+#ifdef CF_BRINGUP   // bring-up builds only (tools/gemm_ts.py, tools/gemm_debug.py): the shipped library carries neither
 #define CF_TS(slot) do { if (P.ts != nullptr && (int)blockIdx.x == P.ts_cta) P.ts[(slot)] = gtime(); } while (0)
+#else
+#define CF_TS(slot) do { } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -292,6 +296,7 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             tc_fence_after();
             if (ep_tid == 0) CF_TS(65 + 4 * t);
             const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * MAX_BN);
+#ifdef CF_BRINGUP
             if (P.dbg != nullptr && blockIdx.x == 0 && t == 0) {
                 for (int c = 0; c < P.BN / 32; ++c) {
                     float v[32];
@@ -305,6 +310,7 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 for (int i = ep_tid; i < MAX_BN * 32; i += 128) P.dbg[16384 + P.C * 64 + i] = sbp[i];
                 if (ep_tid == 0) { P.dbg[16384 + P.C * 64 + MAX_BN * 32] = __uint_as_float(tmem_base); }
             }
+#endif
             if (W32) {
                 // ---- one TMEM pass: the lane's 128 accumulators (4 image rows of 32) ----
                 float v[128];
@@ -561,11 +567,17 @@ bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool) {
     return get_encode_fn() != nullptr;
 }
 
+#ifdef CF_BRINGUP
 static float* g_dbg = nullptr;
 void corr_tcgen05_set_debug(float* p) { g_dbg = p; }
 static unsigned long long* g_ts = nullptr;
 static int g_ts_cta = 0;
 void corr_tcgen05_set_timestamps(unsigned long long* p, int cta) { g_ts = p; g_ts_cta = cta; }
+#else
+static float* const g_dbg = nullptr;            // no process-global mutable state in the shipped library
+static unsigned long long* const g_ts = nullptr;
+static const int g_ts_cta = 0;
+#endif
 
 size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W) {
     return 2 * round_up((size_t)B * C * H * W * sizeof(__nv_bfloat16), 256);

@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     unsigned b = __umulhi(n0, P.hw_magic);
     if (b * (unsigned)P.HW > n0) --b;
     unsigned p = n0 - b * (unsigned)P.HW + lane;
-    if (p >= (unsigned)P.HW) { p -= (unsigned)P.HW; ++b; }      // H*W >= 256 > 32: at most one wrap
+    while (p >= (unsigned)P.HW) { p -= (unsigned)P.HW; ++b; }   // one wrap at most when H*W >= 32; tiny maps (L <= 2) wrap more
     float cx = 0.0f, cy = 0.0f;
     // everything below reads memory the preceding kernels wrote (coords, pyramid) and writes `out`
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__
 
     unsigned b = n0 / HW;
     unsigned p = n0 - b * HW + lane;
-    if (p >= HW) { p -= HW; ++b; }                  // H*W >= 256 > 32: at most one wrap
+    while (p >= HW) { p -= HW; ++b; }               // one wrap at most when H*W >= 32; tiny maps (L <= 2) wrap more
     float cx = 0.0f, cy = 0.0f;
     if (valid) {
         const float inv = __int_as_float((127 - l) << 23);      // 2^-l: the reference's division by 2^l, exactly

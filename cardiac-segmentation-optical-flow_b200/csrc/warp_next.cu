@@ -92,6 +92,25 @@ __global__ void __launch_bounds__(256) warp2d_bwd_kernel(const float* __restrict
     }
 }
 
+// Nearest-mode backward (ATen grid_sampler_2d_backward, nearest): the whole output gradient goes to the nearest texel,
+// the gradient w.r.t. the sampling grid (hence the flow) is zero.
+__global__ void __launch_bounds__(256) warp2d_nearest_bwd_kernel(const float* __restrict__ flow, const float* __restrict__ go,
+                                                                 float* __restrict__ gsrc, int C, int H, int W, float ry,
+                                                                 float rx, long total) {
+    const long t = (long)blockIdx.x * 256 + threadIdx.x;
+    if (t >= total) return;
+    const int x = (int)(t % W);
+    const long row = t / W;
+    const int y = (int)(row % H);
+    const long b = row / H;
+    const size_t HW = (size_t)H * W, pix = (size_t)y * W + x;
+    const float uy = warp_coord(__fadd_rn((float)y, __ldg(flow + (b * 2 + 0) * HW + pix)), (float)(H - 1), ry);
+    const float ux = warp_coord(__fadd_rn((float)x, __ldg(flow + (b * 2 + 1) * HW + pix)), (float)(W - 1), rx);
+    const int ny = __float2int_rn(uy), nx = __float2int_rn(ux);
+    if ((unsigned)ny >= (unsigned)H || (unsigned)nx >= (unsigned)W) return;
+    for (int c = 0; c < C; ++c) atomicAdd(gsrc + (b * C + c) * HW + (size_t)ny * W + nx, __ldg(go + (b * C + c) * HW + pix));
+}
+
 // ---------------------------------------------------------------------------------------------- VecInt
 // out = s*v + warp(s*v, flow = s*v), s a power of two (exact), both channels per thread.
 __global__ void __launch_bounds__(256) vecint_step_kernel(const float* __restrict__ v, float* __restrict__ out,
@@ -168,13 +187,95 @@ __global__ void __launch_bounds__(128) sample_points_kernel(const float* __restr
     }
 }
 
+// Backward of the point sampling: the reference back-propagates an MSE point loss through SpatialTransformerContour into
+// `original` = the predicted flow (training/network_training/SegFlowGaussian.py:1497-1503).  One thread per (b, point):
+// d/d(src) scattered with atomics (two points may share a texel), d/d(locs) written (ATen grid_sampler_2d_backward chained
+// through the reference's 2 * (p / (S - 1) - 0.5): d(u)/d(p) = ((size - 1) / 2) * 2 / (S - 1)).
+template <int MODE>
+__global__ void __launch_bounds__(128) sample_points_bwd_kernel(const float* __restrict__ locs, const float* __restrict__ src,
+                                                                const float* __restrict__ go, float* __restrict__ gsrc,
+                                                                float* __restrict__ glocs, int C, int H, int W, int P,
+                                                                float sn_x, float sn_y, long total) {
+    const long t = (long)blockIdx.x * 128 + threadIdx.x;
+    if (t >= total) return;
+    const long b = t / P;
+    const int p = (int)(t - b * P);
+    const float px = __ldg(locs + (b * 2 + 0) * P + p), py = __ldg(locs + (b * 2 + 1) * P + p);
+    const float nx = __fmul_rn(2.0f, __fsub_rn(__fdiv_rn(px, sn_x), 0.5f));
+    const float ny = __fmul_rn(2.0f, __fsub_rn(__fdiv_rn(py, sn_y), 0.5f));
+    const float ux = __fmul_rn(__fmul_rn(__fadd_rn(nx, 1.0f), 0.5f), (float)(W - 1));
+    const float uy = __fmul_rn(__fmul_rn(__fadd_rn(ny, 1.0f), 0.5f), (float)(H - 1));
+    const size_t HW = (size_t)H * W;
+    if (MODE == CF_MODE_NEAREST) {
+        const int qy = __float2int_rn(uy), qx = __float2int_rn(ux);
+        const bool in = (unsigned)qy < (unsigned)H && (unsigned)qx < (unsigned)W;
+        if (gsrc && in)
+            for (int c = 0; c < C; ++c) atomicAdd(gsrc + (b * C + c) * HW + (size_t)qy * W + qx, __ldg(go + (b * C + c) * P + p));
+        if (glocs) { glocs[(b * 2 + 0) * P + p] = 0.0f; glocs[(b * 2 + 1) * P + p] = 0.0f; }
+        return;
+    }
+    const Tap tp = make_tap(uy, ux);
+    const float fx = floorf(ux), fy = floorf(uy);
+    const float dx_lo = __fsub_rn(__fadd_rn(fx, 1.0f), ux), dx_hi = __fsub_rn(ux, fx);
+    const float dy_lo = __fsub_rn(__fadd_rn(fy, 1.0f), uy), dy_hi = __fsub_rn(uy, fy);
+    const bool y0in = (unsigned)tp.y0 < (unsigned)H, y1in = (unsigned)(tp.y0 + 1) < (unsigned)H;
+    const bool x0in = (unsigned)tp.x0 < (unsigned)W, x1in = (unsigned)(tp.x0 + 1) < (unsigned)W;
+    const size_t o00 = (size_t)tp.y0 * W + tp.x0;
+    float gix = 0.0f, giy = 0.0f;
+    for (int c = 0; c < C; ++c) {
+        const size_t chan = (b * C + c) * HW;
+        const float g = __ldg(go + (b * C + c) * P + p);
+        if (gsrc) {
+            float* gs = gsrc + chan;
+            if (y0in && x0in) atomicAdd(gs + o00, tp.w00 * g);
+            if (y0in && x1in) atomicAdd(gs + o00 + 1, tp.w01 * g);
+            if (y1in && x0in) atomicAdd(gs + o00 + W, tp.w10 * g);
+            if (y1in && x1in) atomicAdd(gs + o00 + W + 1, tp.w11 * g);
+        }
+        if (glocs) {
+            const float* img = src + chan;
+            const float nw = (y0in && x0in) ? __ldg(img + o00) : 0.0f;
+            const float ne = (y0in && x1in) ? __ldg(img + o00 + 1) : 0.0f;
+            const float sw = (y1in && x0in) ? __ldg(img + o00 + W) : 0.0f;
+            const float se = (y1in && x1in) ? __ldg(img + o00 + W + 1) : 0.0f;
+            gix -= nw * dy_lo * g;  giy -= nw * dx_lo * g;
+            gix += ne * dy_lo * g;  giy -= ne * dx_hi * g;
+            gix -= sw * dy_hi * g;  giy += sw * dx_lo * g;
+            gix += se * dy_hi * g;  giy += se * dx_hi * g;
+        }
+    }
+    if (glocs) {
+        glocs[(b * 2 + 0) * P + p] = __fdiv_rn(__fmul_rn(__fmul_rn(gix, __fmul_rn((float)(W - 1), 0.5f)), 2.0f), sn_x);
+        glocs[(b * 2 + 1) * P + p] = __fdiv_rn(__fmul_rn(__fmul_rn(giy, __fmul_rn((float)(H - 1), 0.5f)), 2.0f), sn_y);
+    }
+}
+
 }  // namespace
+
+int launch_sample_points_bwd(const float* locs, const float* src, const float* go, int B, int C, int H, int W, int P, int SH,
+                             int SW, int mode, float* gsrc, float* glocs, cudaStream_t s) {
+    const long total = (long)B * P;
+    const float snx = (float)(SW - 1), sny = (float)(SH - 1);
+    if (mode == CF_MODE_BILINEAR)
+        sample_points_bwd_kernel<CF_MODE_BILINEAR><<<cdiv(total, 128), 128, 0, s>>>(locs, src, go, gsrc, glocs, C, H, W, P, snx, sny, total);
+    else
+        sample_points_bwd_kernel<CF_MODE_NEAREST><<<cdiv(total, 128), 128, 0, s>>>(locs, src, go, gsrc, glocs, C, H, W, P, snx, sny, total);
+    CF_CHECK_LAUNCH("sample_points_bwd_kernel");
+    return CF_OK;
+}
 
 int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W, float* gsrc,
                       float* gflow, cudaStream_t s) {
     const long total = (long)B * H * W;
     warp2d_bwd_kernel<false><<<cdiv(total, 256), 256, 0, s>>>(flow, src, go, gsrc, gflow, C, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
     CF_CHECK_LAUNCH("warp2d_bwd_kernel");
+    return CF_OK;
+}
+
+int launch_warp2d_nearest_bwd(const float* flow, const float* go, int B, int C, int H, int W, float* gsrc, cudaStream_t s) {
+    const long total = (long)B * H * W;
+    warp2d_nearest_bwd_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, go, gsrc, C, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
+    CF_CHECK_LAUNCH("warp2d_nearest_bwd_kernel");
     return CF_OK;
 }
 

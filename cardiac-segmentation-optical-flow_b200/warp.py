@@ -37,14 +37,19 @@ class _Warp2d(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_out):
         f, src = ctx.saved_tensors
-        if ctx.mode != _cabi.MODE_BILINEAR:
-            raise NotImplementedError("backward of the nearest-mode warp is zero almost everywhere; not provided")
         B, C, H, W = src.shape
         go = grad_out.contiguous().float()
         need_flow, need_src = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         gsrc = torch.zeros_like(src) if need_src else None
         gflow = torch.empty_like(f) if need_flow else None
         if ctx.empty:
+            return (gflow.zero_() if need_flow else None), gsrc, None, None
+        if ctx.mode != _cabi.MODE_BILINEAR:
+            # ATen grid_sampler_2d_backward, nearest: the output gradient goes to the nearest texel, the grid gradient is zero
+            if need_src:
+                with torch.cuda.device(src.device):
+                    _cabi.check(_cabi.lib().cf_warp2d_nearest_bwd(f.data_ptr(), go.data_ptr(), B, C, H, W, gsrc.data_ptr(),
+                                                                  _cabi.stream()), "cf_warp2d_nearest_bwd")
             return (gflow.zero_() if need_flow else None), gsrc, None, None
         with torch.cuda.device(src.device):
             _cabi.check(_cabi.lib().cf_warp2d_bwd(f.data_ptr(), src.data_ptr(), go.data_ptr(), B, C, H, W,
@@ -175,6 +180,45 @@ class SpatialTransformer(nn.Module):
         return _Warp2d.apply(flow, original, _MODES[self.mode])
 
 
+class _SamplePoints(torch.autograd.Function):
+    """(locs [B,2,h,P] in pixels, original [B,C,H,W]) -> [B,C,h,P]; differentiable w.r.t. both (the reference back-propagates
+    its MSE point loss through this module into ``original`` = the predicted flow,
+    training/network_training/SegFlowGaussian.py:1497-1503)."""
+
+    @staticmethod
+    def forward(ctx, locs, original, mode, size):
+        lc, src = _cabi.f32c(locs), _cabi.f32c(original)
+        if lc.data_ptr() == locs.data_ptr():
+            lc = lc.clone()                     # the caller normalises its tensor in place afterwards (reference side effect)
+        B, C, H, W = src.shape
+        P = lc.shape[2] * lc.shape[3]
+        out = torch.empty(B, C, lc.shape[2], lc.shape[3], dtype=torch.float32, device=src.device)
+        with torch.cuda.device(src.device):
+            _cabi.check(_cabi.lib().cf_sample_points(lc.data_ptr(), src.data_ptr(), B, C, H, W, P, size[0], size[1], mode,
+                                                     out.data_ptr(), _cabi.stream()), "cf_sample_points")
+        ctx.save_for_backward(lc, src)
+        ctx.mode, ctx.size = mode, size
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        lc, src = ctx.saved_tensors
+        B, C, H, W = src.shape
+        P = lc.shape[2] * lc.shape[3]
+        go = grad_out.contiguous().float()
+        need_locs, need_src = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gsrc = torch.zeros_like(src) if need_src else None
+        glocs = torch.empty_like(lc) if need_locs else None
+        if need_locs or need_src:
+            with torch.cuda.device(src.device):
+                _cabi.check(_cabi.lib().cf_sample_points_bwd(lc.data_ptr(), src.data_ptr(), go.data_ptr(), B, C, H, W, P,
+                                                             ctx.size[0], ctx.size[1], ctx.mode,
+                                                             gsrc.data_ptr() if need_src else None,
+                                                             glocs.data_ptr() if need_locs else None, _cabi.stream()),
+                            "cf_sample_points_bwd")
+        return glocs, gsrc, None, None
+
+
 class SpatialTransformerContour(nn.Module):
     """Samples ``original`` at P points; ``new_locs`` [B,2,1,P] (ch0 = x, ch1 = y, reversed-size
     normalisation as integration.py:23-24).  Like the reference it normalises ``new_locs`` IN PLACE."""
@@ -190,15 +234,9 @@ class SpatialTransformerContour(nn.Module):
         if new_locs.dim() != 4 or new_locs.shape[1] != 2:
             raise ValueError(f"new_locs must be [B, 2, h, P], got {tuple(new_locs.shape)}")
         _cabi.require_cuda(new_locs, original)
-        B, C, H, W = original.shape
-        locs = _cabi.f32c(new_locs)
-        src = _cabi.f32c(original)
-        P = locs.shape[2] * locs.shape[3]
-        out = torch.empty(B, C, locs.shape[2], locs.shape[3], dtype=torch.float32, device=src.device)
-        with torch.cuda.device(src.device):
-            _cabi.check(_cabi.lib().cf_sample_points(locs.data_ptr(), src.data_ptr(), B, C, H, W, P,
-                                                     self.shape[-2], self.shape[-1], _MODES[self.mode], out.data_ptr(), _cabi.stream()),
-                        "cf_sample_points")
+        if original.dim() != 4 or original.shape[0] != new_locs.shape[0]:
+            raise ValueError(f"original must be [B, C, H, W] with B = {new_locs.shape[0]}, got {tuple(original.shape)}")
+        out = _SamplePoints.apply(new_locs, original, _MODES[self.mode], (self.shape[-2], self.shape[-1]))
         # reference side effect (integration.py:23-24): the argument ends up normalised to [-1, 1]
         with torch.no_grad():
             for i in range(2):

@@ -139,8 +139,14 @@ CF_API int cf_warp2d_onehot_argmax_counts(const float* flow, const int64_t* labe
  * (atomics) must be zero-initialised by the caller. */
 CF_API int cf_warp2d_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W,
                   float* grad_src /* zeroed, may be NULL */, float* grad_flow /* may be NULL */, void* stream);
+/* Nearest-mode warp (SpatialTransformer(size, mode='nearest')): the output gradient goes to the nearest texel (grad_src
+ * zeroed by the caller, accumulated with atomics); the gradient w.r.t. the flow is identically zero, as in ATen. */
+CF_API int cf_warp2d_nearest_bwd(const float* flow, const float* grad_out, int B, int C, int H, int W, float* grad_src,
+                          void* stream);
 CF_API int cf_corr_lookup_bwd(const float* coords, const float* grad_out, int B, int H, int W, int L, int r,
-                       float* grad_pyramid /* zeroed, packed like the pyramid */, void* stream);
+                       float* grad_pyramid /* packed like the pyramid; ACCUMULATED into (+=): zero it once, then every
+                                              lookup of the same CorrBlock may add its gradient to the same buffer */,
+                       void* stream);
 CF_API int cf_corr_pool_bwd(float* grad_pyramid, int B, int H, int W, int L, void* stream);
 CF_API int cf_corr_volume_bwd(const float* f1, const float* f2, const float* grad_corr /* level 0 */, int B, int C,
                        int H, int W, float* grad_f1, float* grad_f2, void* stream);
@@ -154,6 +160,13 @@ CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* o
  * with the image's own (H, W); out [B,C,P]. */
 CF_API int cf_sample_points(const float* locs, const float* src, int B, int C, int H, int W, int P, int size_h,
                      int size_w, int mode, float* out, void* stream);
+
+/* Backward of cf_sample_points: the reference back-propagates its MSE point loss through SpatialTransformerContour into
+ * `original` (= the predicted flow; training/network_training/SegFlowGaussian.py:1497-1503).  grad_out [B,C,P];
+ * grad_src [B,C,H,W] accumulates with atomics (zero-initialised by the caller; may be NULL); grad_locs [B,2,P] (gradient
+ * w.r.t. the un-normalised point coordinates; written; may be NULL).  Nearest mode: grad_locs = 0 (as ATen). */
+CF_API int cf_sample_points_bwd(const float* locs, const float* src, const float* grad_out, int B, int C, int H, int W, int P,
+                         int size_h, int size_w, int mode, float* grad_src, float* grad_locs, void* stream);
 
 /* lib/utils.warp (8(f) row 4): replaces `warp(x, flo)` of nnunet/lib/utils.py:29-59 (call site SegFlowGaussian.py:1044).
  * flow [B,2,H,W] with ch0 displacing COLUMNS and ch1 rows; n = 2*(p+f)/max(S-1,1) - 1; grid_sample defaults:

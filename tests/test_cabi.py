@@ -75,17 +75,44 @@ def test_spatial_transformer_module_contract(golden_warp):
     assert list(v.state_dict().keys()) == ["transformer.grid"] and v.scale == 0.125
 
 
-def test_shim_modules_resolve_to_this_package():
-    import importlib.util, os, sys
+def test_shim_import_hook_against_a_regular_package_tree(tmp_path):
+    """The zero-change drop-in: with shim/ on PYTHONPATH (sitecustomize installs the import hook) the reference's OWN import
+    lines resolve to cardioflow_b200 although nnunet / nnunet.lib / nnunet.network_architecture are regular packages with
+    __init__.py files, and BasicUpdateBlock still comes from the tree's own raft_initial.py (SegFlowGaussian.py:35,42)."""
+    import os
+    import subprocess
+    import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for rel, names in (("shim/nnunet/lib/raft_initial.py", ["CorrBlock", "coords_grid"]),
-                       ("shim/nnunet/network_architecture/integration.py",
-                        ["SpatialTransformer", "SpatialTransformerContour", "VecInt"])):
-        spec = importlib.util.spec_from_file_location("shim_" + os.path.basename(rel)[:-3], os.path.join(root, rel))
-        mod = importlib.util.module_from_spec(spec)
-        spec.loader.exec_module(mod)
-        for n in names:
-            assert getattr(mod, n) is getattr(cf, n)
+    tree = tmp_path / "tree"
+    for pkg in ("nnunet", "nnunet/lib", "nnunet/network_architecture"):
+        (tree / pkg).mkdir(parents=True)
+        (tree / pkg / "__init__.py").write_text("")
+    (tree / "nnunet/lib/raft_initial.py").write_text(
+        "class BasicUpdateBlock: origin = 'tree'\nclass CorrBlock: origin = 'tree'\ndef coords_grid(*a, **k): return 'tree'\n")
+    (tree / "nnunet/network_architecture/integration.py").write_text(
+        "class SpatialTransformer: origin = 'tree'\nclass VecInt: origin = 'tree'\nEXTRA = 41\n")
+    prog = (
+        "from nnunet.lib.raft_initial import CorrBlock, BasicUpdateBlock, coords_grid\n"
+        "from nnunet.network_architecture.integration import SpatialTransformer, VecInt, SpatialTransformerContour\n"
+        "import nnunet.network_architecture.integration as integ, nnunet.lib.raft_initial as ri\n"
+        "import cardioflow_b200 as cf\n"
+        "assert CorrBlock is cf.CorrBlock and coords_grid is cf.coords_grid, CorrBlock\n"
+        "assert SpatialTransformer is cf.SpatialTransformer and VecInt is cf.VecInt\n"
+        "assert SpatialTransformerContour is cf.SpatialTransformerContour\n"
+        "assert BasicUpdateBlock.origin == 'tree' and integ.EXTRA == 41\n"
+        "assert ri.__name__ == 'nnunet.lib.raft_initial' and 'shim' in ri.__file__\n"
+        "try:\n    ri.NoSuchThing\nexcept AttributeError: pass\nelse: raise SystemExit('missing names must raise')\n"
+        "print('hook ok')\n")
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([os.path.join(root, "shim"), str(tree)]))
+    r = subprocess.run([sys.executable, "-c", prog], capture_output=True, text=True, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0 and "hook ok" in r.stdout, r.stdout + r.stderr
+    # and a tree WITHOUT raft_initial.py (the upstream state): CorrBlock resolves, BasicUpdateBlock raises a clear ImportError
+    os.remove(tree / "nnunet/lib/raft_initial.py")
+    prog2 = ("from nnunet.lib.raft_initial import CorrBlock, coords_grid\n"
+             "try:\n    from nnunet.lib.raft_initial import BasicUpdateBlock\n"
+             "except ImportError as e: print('clear error:', e)\nelse: raise SystemExit('expected ImportError')\n")
+    r = subprocess.run([sys.executable, "-c", prog2], capture_output=True, text=True, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0 and "clear error" in r.stdout, r.stdout + r.stderr
 
 
 def test_header_is_plain_c_and_a_c_host_links(tmp_path):

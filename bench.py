@@ -58,6 +58,17 @@ ITERS, LEVELS, RADIUS = 12, 4, 4
 METRIC = "frame-pairs/sec (corr+12-iter lookup+warp, 256^2)"
 
 
+def lookup_algorithmic_bytes(b, h, w, num_levels=4, radius=4):
+    """SURVEY.md 8(d) K3, compulsory traffic of one lookup call: out 4*L*K*HW + coords 8*HW + window footprint
+    sum_l 4*HW*min((2r+2)^2, h_l*w_l) per pair (each input read once, each output written once)."""
+    hw, k = h * w, (2 * radius + 1) ** 2
+    foot, hl, wl = 0, h, w
+    for _ in range(num_levels):
+        foot += min((2 * radius + 2) ** 2, hl * wl)
+        hl, wl = hl // 2, wl // 2
+    return b * (4 * num_levels * k * hw + 8 * hw + 4 * hw * foot)
+
+
 # ------------------------------------------------------------------------------------------------ data
 def make_unit(wl, seed, device="cpu", pin=False):
     """Synthetic cine unit (SURVEY.md 8(d) cfg 2 recipe): consecutive frames are shifted/noisy copies."""
@@ -572,7 +583,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp32"])
+    ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "bf16x3", "fp32"],
+                    help="correlation build: auto = fp32-grade like the reference (bf16x3 split on tcgen05, else fp32 CUDA cores); bf16 is opt-in")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying one CUDA graph per step")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -601,7 +613,6 @@ def main():
 
     import cardioflow_b200 as cf
     from cardioflow_b200 import _cabi
-    from oracle import corr_oracle as oracle_meta   # byte/flop formulas only (no compute)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -816,7 +827,7 @@ def main():
             peak, peak_src = json.load(f)["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (copy, read+write)"
     else:
         peak, peak_src = 6650.0, "fallback from B200_PROFILING.md"
-    lookup_bytes = oracle_meta.lookup_algorithmic_bytes(P, H, W, LEVELS, RADIUS)
+    lookup_bytes = lookup_algorithmic_bytes(P, H, W, LEVELS, RADIUS)
     achieved = lookup_bytes / (lookup_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "lookup_traffic.json")
@@ -828,13 +839,16 @@ def main():
     if used_precision == "fp32":
         build_launches = 1 + (LEVELS - 1)
     else:
-        build_launches = 2 + (0 if (W == 32 and LEVELS <= 4) else LEVELS - 2)
+        # version 2 of the build (H % 4 == 0, W % 8 == 0): pre-pass + persistent GEMM (levels 0-2) + one pool launch per further level
+        v2 = H % 4 == 0 and W % 8 == 0
+        build_launches = (2 + max(0, LEVELS - 3)) if v2 else 2 + (0 if (W == 32 and LEVELS <= 4) else LEVELS - 2)
     launches_per_step = (build_launches + ITERS + 1) * n_lanes
 
     line = {
         "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32" if used_precision == "fp32" else "bf16 GEMM (fp32 accumulate) / f32 lookup+warp",
+        "vs_baseline": None, "dtype": {"fp32": "f32", "bf16x3": "f32-grade: bf16x3 split GEMM on tcgen05 (fp32 accumulate) / f32 lookup+warp"}.get(
+            used_precision, "bf16 GEMM (fp32 accumulate) / f32 lookup+warp"),
         "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step_per_gpu": P,
                    "corr_precision": used_precision, "cuda_graph": bool(graphs),

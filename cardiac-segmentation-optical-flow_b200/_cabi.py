@@ -10,10 +10,13 @@ LIB_PATH = os.path.join(PKG, "libcardioflow.so")
 HEADER = os.path.join(os.path.dirname(PKG), "include", "cardioflow.h")
 
 CF_OK, CF_ERR_BAD_ARG, CF_ERR_UNSUPPORTED, CF_ERR_CUDA = 0, -1, -2, -3
-PREC_BF16, PREC_FP32, PREC_AUTO = 0, 1, 2
+PREC_BF16, PREC_FP32, PREC_AUTO, PREC_BF16X3 = 0, 1, 2, 3
+DTYPE_F32, DTYPE_BF16 = 0, 1
+LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
 MODE_BILINEAR, MODE_NEAREST = 0, 1
 BUILD_ALLOW_TILED = 1
-PRECISIONS = {"bf16": PREC_BF16, "fp32": PREC_FP32, "auto": PREC_AUTO}
+PRECISIONS = {"bf16": PREC_BF16, "fp32": PREC_FP32, "auto": PREC_AUTO, "bf16x3": PREC_BF16X3}
+PRECISION_NAMES = {PREC_BF16: "bf16", PREC_FP32: "fp32", PREC_BF16X3: "bf16x3"}
 
 _c = ctypes
 _P, _I, _Z = _c.c_void_p, _c.c_int, _c.c_size_t
@@ -27,6 +30,7 @@ _SIGNATURES = {
     "cf_corr_build_workspace_bytes": (_Z, [_I, _I, _I, _I, _I]),
     "cf_corr_build": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _Z, _c.POINTER(_I), _P]),
     "cf_corr_build_layout": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _Z, _c.POINTER(_I), _c.POINTER(_c.c_uint), _P]),
+    "cf_corr_build_ex": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _Z, _c.POINTER(_I), _c.POINTER(_c.c_uint), _P]),
     "cf_corr_lookup_layout": (_I, [_P, _P, _I, _I, _I, _I, _I, _c.c_uint, _P, _P]),
     "cf_corr_pool": (_I, [_P, _I, _I, _I, _I, _I, _P]),
     "cf_corr_lookup": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),

@@ -52,6 +52,23 @@ def _workspace(device, nbytes):
     return buf
 
 
+def _as_operand(t, precision):
+    """(tensor, CF_DTYPE_*, CF_LAYOUT_*) the builder can read without a host-side copy where possible: bf16 and / or
+    channels_last maps go in as they are (a bf16 channels_last map is already the K-major operand the TMA wants: no pre-pass
+    at all); anything else becomes fp32 NCHW like RAFT's ``.float()``."""
+    t = t.detach()
+    if precision == _cabi.PREC_FP32:                      # the exact CUDA-core mode reads fp32 NCHW only
+        return _cabi.f32c(t), _cabi.DTYPE_F32, _cabi.LAYOUT_NCHW
+    if t.dtype not in (torch.float32, torch.bfloat16):
+        t = t.float()
+    dt = _cabi.DTYPE_BF16 if t.dtype == torch.bfloat16 else _cabi.DTYPE_F32
+    if t.is_contiguous():
+        return t, dt, _cabi.LAYOUT_NCHW
+    if t.is_contiguous(memory_format=torch.channels_last):
+        return t, dt, _cabi.LAYOUT_NHWC
+    return t.contiguous(), dt, _cabi.LAYOUT_NCHW
+
+
 class _CorrBuild(torch.autograd.Function):
     """(fmap1, fmap2) -> packed pyramid.  a2 + a3 of SURVEY.md 8(a)."""
 
@@ -59,7 +76,9 @@ class _CorrBuild(torch.autograd.Function):
     def forward(ctx, fmap1, fmap2, num_levels, precision, pyramid=None, allow_tiled=False, info=None, gstate=None):
         B, C, H, W = fmap1.shape
         lib = _cabi.lib()
-        f1, f2 = _cabi.f32c(fmap1), _cabi.f32c(fmap2)
+        (f1, dt, lay), (f2, dt2, lay2) = _as_operand(fmap1, precision), _as_operand(fmap2, precision)
+        if (dt, lay) != (dt2, lay2):          # mixed inputs: bring both to the reference's fp32 NCHW
+            f1, f2, dt, lay = _cabi.f32c(fmap1), _cabi.f32c(fmap2), _cabi.DTYPE_F32, _cabi.LAYOUT_NCHW
         nfloats = lib.cf_corr_pyramid_bytes(B, H, W, num_levels) // 4
         if pyramid is None:
             pyramid = torch.empty(nfloats, dtype=torch.float32, device=f1.device)
@@ -69,17 +88,20 @@ class _CorrBuild(torch.autograd.Function):
             pyramid = pyramid.view(-1)[:nfloats]
         used = _cabi.ctypes.c_int(-1)
         tiled = _cabi.ctypes.c_uint(0)
-        ws_bytes = lib.cf_corr_build_workspace_bytes(B, C, H, W, precision)
+        zero_copy = dt == _cabi.DTYPE_BF16 and lay == _cabi.LAYOUT_NHWC
+        ws_bytes = 0 if zero_copy else lib.cf_corr_build_workspace_bytes(B, C, H, W, precision)
         ws = _workspace(f1.device, ws_bytes)
         with torch.cuda.device(f1.device):
-            _cabi.check(lib.cf_corr_build_layout(f1.data_ptr(), f2.data_ptr(), B, C, H, W, num_levels, precision,
-                                                 _cabi.BUILD_ALLOW_TILED if allow_tiled else 0, pyramid.data_ptr(),
-                                                 ws.data_ptr() if ws is not None else None, ws_bytes,
-                                                 _cabi.ctypes.byref(used), _cabi.ctypes.byref(tiled), _cabi.stream()),
-                        "cf_corr_build_layout")
+            _cabi.check(lib.cf_corr_build_ex(f1.data_ptr(), f2.data_ptr(), dt, lay, B, C, H, W, num_levels, precision,
+                                             _cabi.BUILD_ALLOW_TILED if allow_tiled else 0, pyramid.data_ptr(),
+                                             ws.data_ptr() if ws is not None else None, ws_bytes,
+                                             _cabi.ctypes.byref(used), _cabi.ctypes.byref(tiled), _cabi.stream()),
+                        "cf_corr_build_ex")
         if info is not None:          # per-call report (thread-safe, unlike a class attribute)
             info["tiled_mask"], info["used_precision"] = tiled.value, used.value
-        ctx.save_for_backward(f1, f2)
+        if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
+            # the backward GEMMs read fp32 NCHW maps (training in the reference is fp32)
+            ctx.save_for_backward(_cabi.f32c(fmap1), _cabi.f32c(fmap2))
         ctx.meta = (B, C, H, W, num_levels)
         ctx.used_precision = used.value
         ctx.gstate = gstate
@@ -152,8 +174,10 @@ class _CorrLookup(torch.autograd.Function):
 class CorrBlock:
     """Drop-in for RAFT's ``CorrBlock(fmap1, fmap2, num_levels=4, radius=4)``; instances are callable.
 
-    ``precision``: "bf16" (tcgen05 tensor cores, fp32 accumulate), "fp32" (CUDA cores, exact-precision mode) or "auto"
-    (default; env ``CARDIOFLOW_CORR_PRECISION``).  ``pyramid_buffer`` / ``out=`` let a caller that loops over
+    ``precision``: "auto" (default; env ``CARDIOFLOW_CORR_PRECISION``) = fp32-grade like the reference: "bf16x3" on the tensor
+    cores (hi/lo bf16 splits, three tcgen05 MMAs per K step, fp32 accumulate, ~1e-6) when the shape allows it, else "fp32"
+    (CUDA cores); "bf16" (one MMA per K step, 2-3e-3 relative error) is opt-in.  Feature maps may be fp32 or bf16, contiguous
+    or ``channels_last`` (a bf16 channels_last map needs no conversion pass at all).  ``pyramid_buffer`` / ``out=`` let a caller that loops over
     frame pairs reuse device memory (the reference allocates afresh every call).  Errors follow torchvision raft.py:368-383 (ValueError).
     """
 
@@ -202,7 +226,7 @@ class CorrBlock:
         self._gstate = {}      # gradient pyramid shared by the backward passes of this block's lookups
         self._pyramid = _CorrBuild.apply(fmap1, fmap2, num_levels, _cabi.PRECISIONS[precision], pyramid_buffer, allow_tiled, info,
                                          self._gstate)
-        self.used_precision = {0: "bf16", 1: "fp32"}.get(info.get("used_precision", -1), "?")
+        self.used_precision = _cabi.PRECISION_NAMES.get(info.get("used_precision", -1), "?")
         self._tiled_mask = info.get("tiled_mask", 0)
         self._views = None
 

@@ -90,54 +90,75 @@ int cf_coords_grid(float* out, int B, int H, int W, void* stream) {
 
 size_t cf_corr_build_workspace_bytes(int B, int C, int H, int W, int precision) {
     if (precision == CF_PREC_FP32 || B < 1 || C < 1 || H < 1 || W < 1) return 0;
-    return (corr_tcgen05_supported(B, C, H, W, false)) ? corr_tcgen05_workspace_bytes(B, C, H, W) : 0;
+    if (corr_tc2_supported(B, C, H, W)) return corr_tc2_workspace_bytes(B, C, H, W, precision != CF_PREC_BF16);
+    return (precision == CF_PREC_BF16 && corr_tcgen05_supported(B, C, H, W, false)) ? corr_tcgen05_workspace_bytes(B, C, H, W) : 0;
 }
 
 int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
                   float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision, void* stream) {
-    return cf_corr_build_layout(f1, f2, B, C, H, W, L, precision, 0, pyramid, workspace, workspace_bytes, used_precision,
-                                nullptr, stream);
+    return cf_corr_build_ex(f1, f2, CF_DTYPE_F32, CF_LAYOUT_NCHW, B, C, H, W, L, precision, 0, pyramid, workspace, workspace_bytes,
+                            used_precision, nullptr, stream);
 }
 
 int cf_corr_build_layout(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision, int flags,
                          float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision,
                          unsigned* tiled_mask, void* stream) {
+    return cf_corr_build_ex(f1, f2, CF_DTYPE_F32, CF_LAYOUT_NCHW, B, C, H, W, L, precision, flags, pyramid, workspace,
+                            workspace_bytes, used_precision, tiled_mask, stream);
+}
+
+int cf_corr_build_ex(const void* f1, const void* f2, int in_dtype, int in_layout, int B, int C, int H, int W, int L,
+                     int precision, int flags, float* pyramid, void* workspace, size_t workspace_bytes,
+                     int* used_precision, unsigned* tiled_mask, void* stream) {
     if (tiled_mask) *tiled_mask = 0;
-    CF_REQUIRE((flags & ~CF_BUILD_ALLOW_TILED) == 0, CF_ERR_BAD_ARG, "cf_corr_build_layout: unknown flags 0x%x", flags);
+    CF_REQUIRE((flags & ~CF_BUILD_ALLOW_TILED) == 0, CF_ERR_BAD_ARG, "cf_corr_build: unknown flags 0x%x", flags);
     CF_REQUIRE(!(flags & CF_BUILD_ALLOW_TILED) || tiled_mask, CF_ERR_BAD_ARG,
-               "cf_corr_build_layout: CF_BUILD_ALLOW_TILED needs tiled_mask to report the layout");
+               "cf_corr_build: CF_BUILD_ALLOW_TILED needs tiled_mask to report the layout");
     CF_REQUIRE(f1 && f2 && pyramid, CF_ERR_BAD_ARG, "cf_corr_build: null pointer");
     CF_REQUIRE(C > 0, CF_ERR_BAD_ARG, "cf_corr_build: C must be positive");
     CF_REQUIRE(((uintptr_t)pyramid & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_build: pyramid must be 256-byte aligned");
-    CF_REQUIRE(precision == CF_PREC_BF16 || precision == CF_PREC_FP32 || precision == CF_PREC_AUTO, CF_ERR_BAD_ARG,
-               "cf_corr_build: unknown precision %d", precision);
+    CF_REQUIRE(precision == CF_PREC_BF16 || precision == CF_PREC_FP32 || precision == CF_PREC_AUTO || precision == CF_PREC_BF16X3,
+               CF_ERR_BAD_ARG, "cf_corr_build: unknown precision %d", precision);
+    CF_REQUIRE(in_dtype == CF_DTYPE_F32 || in_dtype == CF_DTYPE_BF16, CF_ERR_BAD_ARG, "cf_corr_build: unknown in_dtype %d", in_dtype);
+    CF_REQUIRE(in_layout == CF_LAYOUT_NCHW || in_layout == CF_LAYOUT_NHWC, CF_ERR_BAD_ARG, "cf_corr_build: unknown in_layout %d", in_layout);
     LevelDims d;
     int rc = check_corr_shape(B, H, W, L, &d);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     float* levels[CF_MAX_LEVELS] = {};
     for (int l = 0; l < L; ++l) levels[l] = reinterpret_cast<float*>(reinterpret_cast<char*>(pyramid) + d.off[l]);
+    const bool plain = in_dtype == CF_DTYPE_F32 && in_layout == CF_LAYOUT_NCHW;   // what the fp32 SIMT kernel and version 1 read
 
     int from_level = 0;
     int used = CF_PREC_FP32;
     if (precision != CF_PREC_FP32) {
-        // the GEMM fuses as many pooled levels into its epilogue as the shape allows (none .. all)
-        if (corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2)) {
+        const bool want_split = precision != CF_PREC_BF16;
+        if (corr_tc2_supported(B, C, H, W) && aligned16(f1) && aligned16(f2)) {
             int done = 1;
-            rc = launch_corr_tcgen05(f1, f2, B, C, H, W, levels, L, workspace, workspace_bytes, &done,
-                                     (flags & CF_BUILD_ALLOW_TILED) != 0, tiled_mask, s);
+            rc = launch_corr_tc2(f1, f2, in_dtype, in_layout, B, C, H, W, levels, L, want_split, workspace, workspace_bytes, &done,
+                                 (flags & CF_BUILD_ALLOW_TILED) != 0, tiled_mask, s);
+            if (rc) return rc;
+            used = (want_split && in_dtype == CF_DTYPE_F32) ? CF_PREC_BF16X3 : CF_PREC_BF16;
+            from_level = done - 1;
+        } else if (precision == CF_PREC_BF16 && plain && corr_tcgen05_supported(B, C, H, W, false) && aligned16(f1) && aligned16(f2)) {
+            // version 1 (W = 32 register epilogue / generic): shapes version 2 rejects (H % 4 != 0 or W % 8 != 0)
+            int done = 1;
+            rc = launch_corr_tcgen05(reinterpret_cast<const float*>(f1), reinterpret_cast<const float*>(f2), B, C, H, W, levels, L,
+                                     workspace, workspace_bytes, &done, (flags & CF_BUILD_ALLOW_TILED) != 0, tiled_mask, s);
             if (rc) return rc;
             used = CF_PREC_BF16;
             from_level = done - 1;
-        } else if (precision == CF_PREC_BF16) {
+        } else if (precision == CF_PREC_BF16 || precision == CF_PREC_BF16X3 || !plain) {
             return fail(CF_ERR_UNSUPPORTED,
-                        "cf_corr_build: shape B=%d C=%d H=%d W=%d does not fit the tcgen05 tiling "
-                        "(need H*W %% 8 == 0, C %% 16 == 0, C <= 256, 16-byte aligned inputs); use CF_PREC_AUTO or "
-                        "CF_PREC_FP32", B, C, H, W);
+                        "cf_corr_build: shape B=%d C=%d H=%d W=%d does not fit the tcgen05 tiling (need H %% 4 == 0, W %% 8 == 0, "
+                        "C %% 8 == 0, C <= 256, 16-byte aligned inputs); use fp32 NCHW maps with CF_PREC_AUTO or CF_PREC_FP32",
+                        B, C, H, W);
         }
+    } else if (!plain) {
+        return fail(CF_ERR_UNSUPPORTED, "cf_corr_build: CF_PREC_FP32 reads fp32 NCHW feature maps only");
     }
     if (used == CF_PREC_FP32) {
-        rc = launch_corr_simt(f1, f2, B, C, H * W, levels[0], s);
+        rc = launch_corr_simt(reinterpret_cast<const float*>(f1), reinterpret_cast<const float*>(f2), B, C, H * W, levels[0], s);
         if (rc) return rc;
     }
     if (used_precision) *used_precision = used;

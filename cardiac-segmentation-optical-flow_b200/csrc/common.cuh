@@ -110,6 +110,12 @@ int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, i
                         cudaStream_t s);
 size_t corr_tcgen05_workspace_bytes(int B, int C, int H, int W);
 bool corr_tcgen05_supported(int B, int C, int H, int W, bool fuse_pool);
+// version 2 of the tensor-core build (corr_tc2.cu): persistent, swapped roles, bf16 or bf16x3, any input dtype / layout
+bool corr_tc2_supported(int B, int C, int H, int W);
+size_t corr_tc2_workspace_bytes(int B, int C, int H, int W, bool split);
+int launch_corr_tc2(const void* f1, const void* f2, int in_dtype, int in_layout, int B, int C, int H, int W,
+                    float* const* levels, int L, bool split, void* workspace, size_t ws_bytes, int* levels_done,
+                    bool allow_tiled, unsigned* tiled_mask, cudaStream_t s);
 int launch_corr_volume_bwd(const float* f1, const float* f2, const float* gcorr, int B, int C, int HW,
                            float* gf1, float* gf2, cudaStream_t s);
 

@@ -41,7 +41,14 @@ extern "C" {
 /* cf_corr_build precision */
 #define CF_PREC_BF16 0 /* tcgen05.mma kind::f16: feature maps rounded to bf16, fp32 accumulate in TMEM          */
 #define CF_PREC_FP32 1 /* CUDA-core fp32 FMA (exact-precision mode; also serves shapes the TMA path rejects) */
-#define CF_PREC_AUTO 2 /* bf16 tensor-core path when the shape allows it, FP32 otherwise                      */
+#define CF_PREC_AUTO 2 /* fp32-grade: BF16X3 on the tensor cores when the shape allows it, FP32 otherwise       */
+#define CF_PREC_BF16X3 3 /* tcgen05.mma on hi/lo bf16 splits: hi*hi + hi*lo + lo*hi, fp32 accumulate (~1e-6)   */
+
+/* cf_corr_build_ex input element type / memory layout of the feature maps */
+#define CF_DTYPE_F32 0
+#define CF_DTYPE_BF16 1
+#define CF_LAYOUT_NCHW 0 /* [B, C, H, W] contiguous (what the reference's encoders emit)                        */
+#define CF_LAYOUT_NHWC 1 /* [B, H, W, C] contiguous = torch.channels_last storage; already K-major for the MMA  */
 
 /* cf_warp2d interpolation */
 #define CF_MODE_BILINEAR 0
@@ -69,7 +76,7 @@ CF_API int cf_coords_grid(float* out, int B, int H, int W, void* stream);
  * f1, f2 [B,C,H,W] fp32.  Writes all L levels into `pyramid` (cf_corr_pyramid_bytes).
  * `workspace` (256-byte aligned, cf_corr_build_workspace_bytes; may be NULL when that is 0) holds the bf16
  * copies of the feature maps for the tensor-core path.
- * `used_precision` (optional) receives the precision actually used (CF_PREC_BF16 / CF_PREC_FP32). */
+ * `used_precision` (optional) receives the precision actually used (CF_PREC_BF16 / CF_PREC_FP32 / CF_PREC_BF16X3). */
 CF_API size_t cf_corr_build_workspace_bytes(int B, int C, int H, int W, int precision);
 CF_API int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision,
                   float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision, void* stream);
@@ -83,6 +90,15 @@ CF_API int cf_corr_build(const float* f1, const float* f2, int B, int C, int H, 
 CF_API int cf_corr_build_layout(const float* f1, const float* f2, int B, int C, int H, int W, int L, int precision, int flags,
                          float* pyramid, void* workspace, size_t workspace_bytes, int* used_precision,
                          unsigned* tiled_mask, void* stream);
+/* Full form.  `in_dtype` / `in_layout` describe f1 and f2 (CF_DTYPE_*, CF_LAYOUT_*): bf16 channels-last maps are read by
+ * the TMA directly (no pre-pass, no workspace); every other combination goes through one conversion pass into `workspace`
+ * (cf_corr_build_workspace_bytes).  The reference computes this volume in fp32 (RAFT casts the maps with .float();
+ * SegFlowGaussian.py:2909 runs without autocast), so CF_PREC_AUTO selects the fp32-grade tensor-core mode CF_PREC_BF16X3;
+ * plain CF_PREC_BF16 (2-3e-3 relative error) is opt-in.  A bf16 input has no low part: BF16X3 degrades to BF16 and
+ * `used_precision` says so. */
+CF_API int cf_corr_build_ex(const void* f1, const void* f2, int in_dtype, int in_layout, int B, int C, int H, int W, int L,
+                     int precision, int flags, float* pyramid, void* workspace, size_t workspace_bytes,
+                     int* used_precision, unsigned* tiled_mask, void* stream);
 CF_API int cf_corr_lookup_layout(const float* pyramid, const float* coords, int B, int H, int W, int L, int r,
                           unsigned tiled_mask, float* out, void* stream);
 

@@ -192,10 +192,11 @@ def test_full_size_properties_cfg4():
     assert np.abs(blk(coords)[:1].cpu().numpy() - want).max() <= 2e-5 * np.abs(want).max()
 
 
-@pytest.mark.parametrize("hw,c,want_mask", [((64, 64), 128, 2), ((32, 64), 64, 2), ((64, 32), 256, 1), ((40, 96), 32, 0), ((64, 128), 32, 0)])
+@pytest.mark.parametrize("hw,c,want_mask", [((64, 64), 128, 3), ((32, 64), 64, 3), ((64, 32), 256, 1), ((40, 96), 32, 3), ((64, 128), 32, 3),
+                                            ((36, 72), 40, 1), ((16, 16), 64, 0)])
 def test_tiled_levels_generic_epilogue(monkeypatch, hw, c, want_mask):
-    """Widths other than 32: the fused level 1 is tiled by addressing when its rows are >= 128 B and the pooling chain reads
-    the tiled level; pyramids and lookups must be bit-identical to the row-major build."""
+    """Any width (version 2 of the build stores from registers, tiling is address arithmetic): level 0 is tiled when its rows
+    are >= 128 B, level 1 likewise (W >= 64, H % 8 == 0); pyramids and lookups must be bit-identical to the row-major build."""
     h, w = hw
     g = torch.Generator().manual_seed(h * w + c)
     f1, f2 = torch.randn(2, c, h, w, generator=g).to(DEV), torch.randn(2, c, h, w, generator=g).to(DEV)

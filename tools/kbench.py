@@ -98,7 +98,7 @@ if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24", "cfg2h", "cfg2q"):
     outs = [torch.empty(P, L * 81, H, W, device=dev) for _ in range(nrot)]
     HWn = H * W
     blks = {}
-    for prec in ("bf16", "fp32"):
+    for prec in ("bf16", "bf16x3", "fp32"):
         if not want("build_" + prec):
             continue
         us, mn = timeit(lambda i: blks.__setitem__(i, cf.CorrBlock(f1[i], f2[i], precision=prec, pyramid_buffer=pyr[i])), nrot,
@@ -107,7 +107,7 @@ if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24", "cfg2h", "cfg2q"):
         nb = P * (2 * C * HWn * 4 + 4 * HWn * lv)
         report(f"corr_build[{prec}] (gemm+pyramid)", us, mn, nb, 2.0 * P * HWn * HWn * C)
     for i in range(nrot):
-        blks[i] = cf.CorrBlock(f1[i], f2[i], precision="fp32", pyramid_buffer=pyr[i])
+        blks[i] = cf.CorrBlock(f1[i], f2[i], precision=os.environ.get("KB_LOOKUP_PREC", "bf16"), pyramid_buffer=pyr[i])
     from oracle.corr_oracle import lookup_algorithmic_bytes
     lb = lookup_algorithmic_bytes(P, H, W, L, R)
     if want("lookup"):

@@ -39,6 +39,10 @@ _SIGNATURES = {
     "cf_fmap_pyramid_bytes": (_Z, [_I, _I, _I, _I, _I]),
     "cf_fmap_pyramid_build": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "cf_corr_lookup_fused": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    "cf_corr_otf_supported": (_I, [_I, _I, _I, _I, _I]),
+    "cf_corr_otf_operand_bytes": (_Z, [_I, _I, _I, _I, _I]),
+    "cf_corr_otf_prepare": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _Z, _P]),
+    "cf_corr_lookup_otf": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "cf_warp2d": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "cf_warp2d_taps": (_I, [_P, _I, _I, _I, _P, _P]),
     "cf_warp2d_onehot_argmax": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),

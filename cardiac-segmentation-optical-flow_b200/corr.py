@@ -211,10 +211,20 @@ class CorrBlock:
             f2 = _cabi.f32c(fmap2)
             self._f2_pyramid = torch.empty(lib.cf_fmap_pyramid_bytes(B, C, H, W, num_levels) // 4, dtype=torch.float32,
                                            device=f2.device)
+            # tensor-core variant (tcgen05, bf16 operands) when the shape fits and fp32 was not asked for; else the fp32 CUDA-core one
+            self._otf_tc = precision != "fp32" and bool(lib.cf_corr_otf_supported(B, C, H, W, num_levels))
             with torch.cuda.device(f2.device):
-                _cabi.check(lib.cf_fmap_pyramid_build(f2.data_ptr(), B, C, H, W, num_levels,
-                                                      self._f2_pyramid.data_ptr(), _cabi.stream()), "cf_fmap_pyramid_build")
-            self.used_precision = "fp32"
+                if self._otf_tc:
+                    self._operands = torch.empty(lib.cf_corr_otf_operand_bytes(B, C, H, W, num_levels), dtype=torch.uint8,
+                                                 device=f2.device)
+                    _cabi.check(lib.cf_corr_otf_prepare(self._f1.data_ptr(), f2.data_ptr(), B, C, H, W, num_levels,
+                                                        self._operands.data_ptr(), self._f2_pyramid.data_ptr(),
+                                                        self._f2_pyramid.numel() * 4, _cabi.stream()), "cf_corr_otf_prepare")
+                    self._f2_pyramid = None        # scratch of the preparation only
+                else:
+                    _cabi.check(lib.cf_fmap_pyramid_build(f2.data_ptr(), B, C, H, W, num_levels,
+                                                          self._f2_pyramid.data_ptr(), _cabi.stream()), "cf_fmap_pyramid_build")
+            self.used_precision = "bf16" if self._otf_tc else "fp32"
             self._pyramid = None
             self._tiled_mask = 0
             return
@@ -290,6 +300,10 @@ class CorrBlock:
         elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous():
             raise ValueError(f"out must be a contiguous fp32 tensor of shape {shape}")
         with torch.cuda.device(c.device):
+            if self._otf_tc:
+                _cabi.check(_cabi.lib().cf_corr_lookup_otf(self._operands.data_ptr(), c.data_ptr(), B, self._f1.shape[1], H, W,
+                                                           L, r, out.data_ptr(), _cabi.stream()), "cf_corr_lookup_otf")
+                return out
             _cabi.check(_cabi.lib().cf_corr_lookup_fused(self._f1.data_ptr(), self._f2_pyramid.data_ptr(), c.data_ptr(),
                                                          B, self._f1.shape[1], H, W, L, r, out.data_ptr(),
                                                          _cabi.stream()), "cf_corr_lookup_fused")

@@ -260,6 +260,37 @@ int cf_corr_lookup_fused(const float* f1, const float* f2_pyramid, const float* 
     return launch_lookup_fused(f1, f2_pyramid, coords, B, C, H, W, L, r, out, (cudaStream_t)stream);
 }
 
+// ---- on-the-fly lookup on the tensor cores (K4, tcgen05) ----------------------------------------------------------
+int cf_corr_otf_supported(int B, int C, int H, int W, int L) { return lookup_tc_supported(B, C, H, W, L) ? 1 : 0; }
+
+size_t cf_corr_otf_operand_bytes(int B, int C, int H, int W, int L) {
+    return lookup_tc_supported(B, C, H, W, L) ? lookup_tc_operand_bytes(B, C, H, W, L) : 0;
+}
+
+int cf_corr_otf_prepare(const float* f1, const float* f2, int B, int C, int H, int W, int L, void* operands, void* workspace,
+                        size_t workspace_bytes, void* stream) {
+    CF_REQUIRE(f1 && f2 && operands, CF_ERR_BAD_ARG, "cf_corr_otf_prepare: null pointer");
+    CF_REQUIRE(((uintptr_t)operands & 255u) == 0, CF_ERR_BAD_ARG, "cf_corr_otf_prepare: operands must be 256-byte aligned");
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    CF_REQUIRE(C > 0 && lookup_tc_supported(B, C, H, W, L), CF_ERR_UNSUPPORTED,
+               "cf_corr_otf_prepare: shape B=%d C=%d H=%d W=%d needs H %% 8 == 0, W %% 16 == 0, C %% 8 == 0, C <= 256 "
+               "(cf_corr_lookup_fused serves every other shape)", B, C, H, W);
+    return launch_lookup_tc_prepare(f1, f2, B, C, H, W, L, operands, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int cf_corr_lookup_otf(const void* operands, const float* coords, int B, int C, int H, int W, int L, int r, float* out,
+                       void* stream) {
+    CF_REQUIRE(operands && coords && out, CF_ERR_BAD_ARG, "cf_corr_lookup_otf: null pointer");
+    CF_REQUIRE(r >= 1 && r <= CF_MAX_RADIUS, CF_ERR_UNSUPPORTED, "cf_corr_lookup_otf: radius %d not in [1,%d]", r, CF_MAX_RADIUS);
+    LevelDims d;
+    int rc = check_corr_shape(B, H, W, L, &d);
+    if (rc) return rc;
+    CF_REQUIRE(C > 0 && lookup_tc_supported(B, C, H, W, L), CF_ERR_UNSUPPORTED, "cf_corr_lookup_otf: unsupported shape");
+    return launch_lookup_tc(operands, coords, B, C, H, W, L, r, out, (cudaStream_t)stream);
+}
+
 // ---- 8(f) rows: backward passes, VecInt, point sampling -------------------------------------------------------
 int cf_warp2d_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W,
                   float* grad_src, float* grad_flow, void* stream) {

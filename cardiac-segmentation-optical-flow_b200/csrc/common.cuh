@@ -148,4 +148,12 @@ bool fmap_level_dims(int B, int C, int H, int W, int L, LevelDims* d);
 int launch_fmap_pyramid(const float* f2, int B, int C, int H, int W, int L, float* f2pyr, cudaStream_t s);
 int launch_lookup_fused(const float* f1, const float* f2pyr, const float* coords, int B, int C, int H, int W,
                         int L, int r, float* out, cudaStream_t s);
+
+// on-the-fly lookup on the tensor cores (lookup_tc.cu): operands = bf16 channels-last f1 + pooled f2 levels
+bool lookup_tc_supported(int B, int C, int H, int W, int L);
+size_t lookup_tc_operand_bytes(int B, int C, int H, int W, int L);
+int launch_lookup_tc_prepare(const float* f1, const float* f2, int B, int C, int H, int W, int L, void* operands, void* workspace,
+                             size_t ws_bytes, cudaStream_t s);
+int launch_lookup_tc(const void* operands, const float* coords, int B, int C, int H, int W, int L, int r, float* out,
+                     cudaStream_t s);
 }  // namespace cf

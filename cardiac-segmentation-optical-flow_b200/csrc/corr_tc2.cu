@@ -24,8 +24,8 @@
 //     freed staging memory is what makes the doubled operands fit.
 //   * inputs may be fp32 or bf16, NCHW or channels-last; bf16 channels-last maps feed the TMA directly (no pre-pass).
 //
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-9 = epilogue (two warps per TMEM
-// lane quadrant, 64 queries each).  The 128-query block (K-major, SWIZZLE_128B) stays resident in shared memory while
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-17 = epilogue (four warps per TMEM
+// lane quadrant, 32 queries each).  The 128-query block (K-major, SWIZZLE_128B) stays resident in shared memory while
 // the q tiles stream through a ring; fp32 accumulators are double-buffered in TMEM.
 #include <cstdlib>
 #include <mutex>
@@ -96,7 +96,8 @@ using namespace tc;
 constexpr int TQ = 128;          // fmap2 positions per tile (UMMA M): 4 rows x 32 columns
 constexpr int NP = 128;          // queries per block (UMMA N)
 constexpr int BK = 64, UK = 16;  // channels per ring stage / per MMA
-constexpr int EPI_WARPS = 8;
+constexpr int EPI_WARPS = 16;         // four per TMEM lane quadrant
+constexpr int EPQ = NP * 4 / EPI_WARPS;   // queries per epilogue warp (32: one tcgen05.ld x32)
 constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
 constexpr int TMEM_COLS = 2 * NP;   // two accumulators
 constexpr int MAX_KB = 4;           // C <= 256
@@ -121,6 +122,8 @@ struct G2Params {
     long units;          // B * PB * QT
     float div, mul;      // sqrt(C); 1/sqrt(C) when exact (power of two), else 0
     int tile_l0, tile_l1;
+    int sched;           // 0: contiguous shares of all units, 1: whole keys round-robin (see the kernel)
+    int skip;            // bring-up timing knob (CF_TC2_SKIP): bit 0 no level-0 stores, bit 1 no level 1, bit 2 no level 2
 };
 
 __device__ __forceinline__ float pool4(float a, float b, float c, float d) {
@@ -146,9 +149,18 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
     auto ring = [&](int stage, int part) { return s_ring + (uint32_t)stage * K::STAGE_BYTES + (uint32_t)part * OP_BYTES; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // contiguous share of the (pair, query block, q tile) units; q tile fastest, so a CTA reloads its query block rarely
+    // Work of this CTA, as a sequence of (key = pair * PB + query block, q tile) units with the q tile fastest:
+    //   sched 0: a contiguous 1/gridDim share of all units (equal shares; a CTA reloads its query block 2-3 times);
+    //   sched 1: whole keys dealt round-robin -- at any time the CTAs work on neighbouring keys, i.e. on a few pairs, so the
+    //            fmap2 operand they all re-read stays in L2 when the batch's operands exceed it (cfg4: 134 MB).
     const long u_begin = P.units * (long)blockIdx.x / (long)gridDim.x;
-    const long u_end = P.units * ((long)blockIdx.x + 1) / (long)gridDim.x;
+    const long n_keys = (long)P.B * P.PB;
+    const long n_it = P.sched == 0 ? P.units * ((long)blockIdx.x + 1) / (long)gridDim.x - u_begin
+                                   : ((n_keys - (long)blockIdx.x + (long)gridDim.x - 1) / (long)gridDim.x) * P.QT;
+    auto unit_at = [&](long it, long& key, int& qt) {
+        if (P.sched == 0) { const long u = u_begin + it; key = u / P.QT; qt = (int)(u - key * P.QT); }
+        else { const long kq = it / P.QT; key = (long)blockIdx.x + kq * (long)gridDim.x; qt = (int)(it - kq * P.QT); }
+    };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NSTAGE; ++s) { mbar_init(bar(kFull + s), 1); mbar_init(bar(kEmpty + s), 1); }
@@ -171,9 +183,10 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
         if (lane == 0) {
             int stage = 0, phase = 0, n_res = 0;
             long cur_key = -1;
-            for (long u = u_begin; u < u_end; ++u) {
-                const int qt = (int)(u % P.QT);
-                const long key = u / P.QT;                 // b * PB + pb
+            for (long it = 0; it < n_it; ++it) {
+                long key;                                  // b * PB + pb
+                int qt;
+                unit_at(it, key, qt);
                 const int pb = (int)(key % P.PB), b = (int)(key / P.PB);
                 if (key != cur_key) {
                     // the MMAs of the previous query block must have retired before its operand is overwritten
@@ -192,6 +205,10 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
                     mbar_expect_tx(bar(kFull + stage), K::STAGE_BYTES);
                     // four boxes (64 channels, 8 x, 4 y) = 32 rows = 4 KB each: smem row = 32 * x-block + 8 * y + x (= TMEM lane);
                     // x-blocks beyond the map are zero-filled
+                    if (P.skip & 8) {     // timing experiment: ONE 3-D box of 128 consecutive positions (results are wrong)
+                        tma_load_3d(ring(stage, 0), &tmPh, bar(kFull + stage), kb * BK, qt * 128, b);
+                        if (SPLIT) tma_load_3d(ring(stage, 1), &tmPl, bar(kFull + stage), kb * BK, qt * 128, b);
+                    } else
 #pragma unroll
                     for (int xb = 0; xb < 4; ++xb) {
                         tma_load_4d(ring(stage, 0) + (uint32_t)xb * 4096u, &tmQh, bar(kFull + stage), kb * BK, 32 * tx + 8 * xb, 4 * ty, b);
@@ -209,8 +226,10 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
             int stage = 0, phase = 0, n_res = 0;
             long cur_key = -1;
             long t = 0;
-            for (long u = u_begin; u < u_end; ++u, ++t) {
-                const long key = u / P.QT;
+            for (long it = 0; it < n_it; ++it, ++t) {
+                long key;
+                int qt_unused;
+                unit_at(it, key, qt_unused);
                 if (key != cur_key) {
                     mbar_wait(bar(kPFull), (uint32_t)(n_res & 1));
                     ++n_res;
@@ -239,32 +258,35 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
                     if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(bar(kAccFull + acc));
-                if (u + 1 == u_end || (u + 1) / P.QT != key) umma_commit(bar(kPEmpty));   // last use of this query block
+                long next_key = -1;
+                if (it + 1 < n_it) unit_at(it + 1, next_key, qt_unused);
+                if (next_key != key) umma_commit(bar(kPEmpty));   // last use of this query block
             }
         }
     } else {
         // ===================== epilogue warps =====================
         const int quad = warp & 3;                 // TMEM lane quadrant this warp may read = x-block of the q tile
-        const int half = (warp - 2) >> 2;          // which 64 of the 128 queries
+        const int part = (warp - 2) >> 2;          // which EPQ of the 128 queries
         const int r = lane >> 3, c = lane & 7;     // position of this lane's q inside the quadrant's 4 x 8 block
         const int W = P.W, HW = P.HW;
         const int w1 = W >> 1, w2 = W >> 2;
-        const size_t img1 = (size_t)(P.H >> 1) * w1, img2 = (size_t)(P.H >> 2) * w2;
-        const bool a1 = ((r | c) & 1) == 0;                    // lane holds a level-1 result
-        const bool a2 = r == 0 && (c & 3) == 0;                // lane holds a level-2 result
+        const unsigned img1 = (unsigned)((P.H >> 1) * w1), img2 = (unsigned)((P.H >> 2) * w2);
+        const bool K0 = (c & 1) != 0, K1 = (r & 1) != 0;       // position of this lane's q inside its 2x2 block
+        const int kk = (K1 ? 2 : 0) + (K0 ? 1 : 0);
+        const bool B0 = (c & 2) != 0, B1 = (r & 2) != 0;       // position of that 2x2 block inside its 4x4 block
+        const bool do1 = P.level1 != nullptr && !(P.skip & 2), do2 = do1 && P.level2 != nullptr && !(P.skip & 4);
         long t = 0;
-        for (long u = u_begin; u < u_end; ++u, ++t) {
-            const int qt = (int)(u % P.QT);
-            const long key = u / P.QT;
+        for (long it = 0; it < n_it; ++it, ++t) {
+            long key;
+            int qt;
+            unit_at(it, key, qt);
             const int pb = (int)(key % P.PB), b = (int)(key / P.PB);
             const int ty = qt / P.qt_x, tx = qt - ty * P.qt_x;
             const int acc = (int)(t & 1);
             mbar_wait(bar(kAccFull + acc), (uint32_t)((t >> 1) & 1));
             tc_fence_after();
-            const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NP + half * 64);
-            float v[64];
-            tmem_ld32(tacc, v);
-            tmem_ld32(tacc + 32u, v + 32);
+            float v[EPQ];
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NP + part * EPQ), v);
             tmem_wait_ld();
             // the accumulator is in registers: hand the TMEM buffer back to the MMA warp right away
             tc_fence_before();
@@ -272,41 +294,62 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
             if (lane == 0) mbar_arrive(bar(kAccEmpty + acc));
 
             const int x0 = 32 * tx + 8 * quad;
-            const bool quad_ok = x0 < W;                        // warp-uniform (W is a multiple of 8)
             const int y = 4 * ty + r, x = x0 + c;
-            const int p_first = pb * NP + half * 64;            // first query of this warp's 64
-            const int n_valid = min(64, HW - p_first);          // warp-uniform; <= 0 when the block hangs over the map
-            if (!quad_ok || n_valid <= 0) continue;
+            const int p_first = pb * NP + part * EPQ;           // first query of this warp's share
+            const int n_valid = min(EPQ, HW - p_first);         // warp-uniform; <= 0 when the block hangs over the map
+            if (x0 >= W || n_valid <= 0) continue;              // warp-uniform (W is a multiple of 8)
             const size_t q0 = P.tile_l0 ? (size_t)(((y >> 2) * (W >> 2) + (x >> 2)) * 16 + (y & 3) * 4 + (x & 3))
                                         : (size_t)y * W + x;
             const int y1 = y >> 1, x1 = x >> 1;
             const size_t q1 = P.tile_l1 ? (size_t)(((y1 >> 2) * (w1 >> 2) + (x1 >> 2)) * 16 + (y1 & 3) * 4 + (x1 & 3))
                                         : (size_t)y1 * w1 + x1;
             const size_t q2 = (size_t)(y >> 2) * w2 + (x >> 2);
-            const size_t img = (size_t)b * HW + p_first;        // first image (query) index
-            float* o0 = P.level0 + img * HW + q0;
-            float* o1 = P.level1 ? P.level1 + img * img1 + q1 : nullptr;
-            float* o2 = P.level2 ? P.level2 + img * img2 + q2 : nullptr;
-            const bool do1 = o1 != nullptr, do2 = o2 != nullptr;
+            const size_t img = (size_t)b * HW + p_first;        // first image (query) index of this warp
+            float* const o0 = P.level0 + img * HW + q0;
+            float* const o1 = do1 ? P.level1 + img * img1 + q1 : nullptr;
+            float* const o2 = do2 ? P.level2 + img * img2 + q2 : nullptr;
+            // Straight-line code over the warp's queries (no branch inside: the 32 shuffle / add chains interleave);
+            // stores are predicated, everything else is computed for all lanes.
+            if (P.mul != 0.0f) {
 #pragma unroll
-            for (int j = 0; j < 64; ++j) {
-                if (j < n_valid) {                               // warp-uniform
-                    const float val = P.mul != 0.0f ? __fmul_rn(v[j], P.mul) : __fdiv_rn(v[j], P.div);
-                    o0[(size_t)j * HW] = val;
-                    if (do1) {
-                        // 2x2 mean over (y, x) of this query's image: the lane at even (r, c) sums itself, +1, +8, +9
-                        const float vb = __shfl_down_sync(0xffffffffu, val, 1);
-                        const float vc = __shfl_down_sync(0xffffffffu, val, 8);
-                        const float vd = __shfl_down_sync(0xffffffffu, val, 9);
-                        const float l1 = pool4(val, vb, vc, vd);
-                        if (a1) o1[(size_t)j * img1] = l1;
-                        if (do2) {
-                            const float lb = __shfl_down_sync(0xffffffffu, l1, 2);
-                            const float lc = __shfl_down_sync(0xffffffffu, l1, 16);
-                            const float ld = __shfl_down_sync(0xffffffffu, l1, 18);
-                            const float l2 = pool4(l1, lb, lc, ld);
-                            if (a2) o2[(size_t)j * img2] = l2;
-                        }
+                for (int j = 0; j < EPQ; ++j) v[j] = __fmul_rn(v[j], P.mul);
+            } else {
+#pragma unroll
+                for (int j = 0; j < EPQ; ++j) v[j] = __fdiv_rn(v[j], P.div);
+            }
+            if (!(P.skip & 1)) {
+#pragma unroll
+                for (int j = 0; j < EPQ; ++j)
+                    if (j < n_valid) o0[(unsigned)j * (unsigned)HW] = v[j];
+            }
+            if (do1) {
+                // 2x2 mean over (y, x) of a query's image, in avg_pool2d's order ((a+b)+c)+d.  The four lanes of a 2x2 block
+                // exchange round-robin: for every group of four queries each lane ends up with all four values of ITS block
+                // for ONE of the four queries (the one matching its position in the block), so three shuffles serve four
+                // queries (a plain "+1, +8, +9" gather needs three per query and uses a quarter of the lanes).
+#pragma unroll
+                for (int g = 0; g < EPQ / 4; ++g) {
+                    const float v0 = v[4 * g], v1 = v[4 * g + 1], v2 = v[4 * g + 2], v3 = v[4 * g + 3];
+                    const float t0 = K0 ? v1 : v0, t1 = K0 ? v0 : v1, u0 = K0 ? v3 : v2, u1 = K0 ? v2 : v3;
+                    const float own = K1 ? u0 : t0;                                        // my value of query 4g + kk
+                    const float r1 = __shfl_xor_sync(0xffffffffu, K1 ? u1 : t1, 1);        // x neighbour's value of MY query
+                    const float r2 = __shfl_xor_sync(0xffffffffu, K1 ? t0 : u0, 8);        // y neighbour's
+                    const float r3 = __shfl_xor_sync(0xffffffffu, K1 ? t1 : u1, 9);        // diagonal neighbour's
+                    const float x0 = K1 ? r2 : own, x1 = K1 ? r3 : r1;                     // top row: my column, other column
+                    const float y0 = K1 ? own : r2, y1 = K1 ? r1 : r3;                     // bottom row
+                    const float l1 = pool4(K0 ? x1 : x0, K0 ? x0 : x1, K0 ? y1 : y0, K0 ? y0 : y1);
+                    const bool ok = 4 * g + kk < n_valid;
+                    if (ok) o1[(unsigned)(4 * g + kk) * img1] = l1;
+                    if (do2) {
+                        // the same exchange between the four 2x2 blocks of a 4x4 block (lanes of equal block position hold
+                        // level-1 values of the same query)
+                        const float q1 = __shfl_xor_sync(0xffffffffu, l1, 2);
+                        const float q2 = __shfl_xor_sync(0xffffffffu, l1, 16);
+                        const float q3 = __shfl_xor_sync(0xffffffffu, l1, 18);
+                        const float s0 = B1 ? q2 : l1, s1 = B1 ? q3 : q1;
+                        const float z0 = B1 ? l1 : q2, z1 = B1 ? q1 : q3;
+                        const float l2 = pool4(B0 ? s1 : s0, B0 ? s0 : s1, B0 ? z1 : z0, B0 ? z0 : z1);
+                        if (ok && !B0 && !B1) o2[(unsigned)(4 * g + kk) * img2] = l2;
                     }
                 }
             }
@@ -331,9 +374,9 @@ template <typename TIn>
 __global__ void __launch_bounds__(256) prep_transpose_kernel(const TIn* __restrict__ a, const TIn* __restrict__ b,
                                                              __nv_bfloat16* __restrict__ ha, __nv_bfloat16* __restrict__ hb,
                                                              __nv_bfloat16* __restrict__ la, __nv_bfloat16* __restrict__ lb,
-                                                             int C, int HW) {
+                                                             int C, int HW, int nmaps) {
     __shared__ float tile[64][65];
-    const int which = blockIdx.z & 1, bi = blockIdx.z >> 1;
+    const int which = nmaps == 2 ? (blockIdx.z & 1) : 0, bi = nmaps == 2 ? (blockIdx.z >> 1) : blockIdx.z;
     const TIn* src = (which ? b : a) + (size_t)bi * C * HW;
     __nv_bfloat16* hi = (which ? hb : ha) + (size_t)bi * HW * C;
     __nv_bfloat16* lo = (which ? lb : la);
@@ -399,6 +442,8 @@ size_t part_bytes(int B, int C, int HW) { return round_up((size_t)B * C * HW * s
 }  // namespace
 
 bool corr_tc2_supported(int B, int C, int H, int W) {
+    static const bool force_v1 = [] { const char* e = getenv("CF_FORCE_V1"); return e && atoi(e) != 0; }();   // A/B knob
+    if (force_v1) return false;
     if (B < 1 || C < 8 || C % 8 != 0 || C > 64 * MAX_KB || H < 4 || H % 4 != 0 || W < 8 || W % 8 != 0) return false;
     if ((long)H * W > (1L << 24)) return false;
     return tmap_encode_fn() != nullptr;
@@ -433,10 +478,10 @@ int corr_tc2_prepare(const void* f1, const void* f2, int in_dtype, int in_layout
         const dim3 grid((unsigned)cdiv(HW, 64), (unsigned)cdiv(C, 64), (unsigned)(2 * B));
         if (in_dtype == CF_DTYPE_F32)
             prep_transpose_kernel<float><<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(f1), reinterpret_cast<const float*>(f2),
-                                                              o1, o2, p1, p2, C, HW);
+                                                              o1, o2, p1, p2, C, HW, 2);
         else
             prep_transpose_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(f1),
-                                                                      reinterpret_cast<const __nv_bfloat16*>(f2), o1, o2, p1, p2, C, HW);
+                                                                      reinterpret_cast<const __nv_bfloat16*>(f2), o1, o2, p1, p2, C, HW, 2);
         CF_CHECK_LAUNCH("prep_transpose_kernel");
     } else {   // fp32 channels-last
         const size_t n4 = (size_t)B * C * HW / 4;   // C % 8 == 0
@@ -446,6 +491,16 @@ int corr_tc2_prepare(const void* f1, const void* f2, int in_dtype, int in_layout
         CF_CHECK_LAUNCH("prep_convert_kernel");
     }
     *h1 = o1; *h2 = o2; *l1 = p1; *l2 = p2;
+    return CF_OK;
+}
+
+// one fp32 [B, C, HW] map -> bf16 [B, HW, C] (operands of the on-the-fly lookup, lookup_tc.cu)
+int launch_prep_transpose_one(const float* src, void* dst_bf16, int B, int C, int HW, cudaStream_t s) {
+    if (B > 65535) return fail(CF_ERR_UNSUPPORTED, "prep: batch %d > 65535", B);
+    const dim3 grid((unsigned)cdiv(HW, 64), (unsigned)cdiv(C, 64), (unsigned)B);
+    prep_transpose_kernel<float><<<grid, 256, 0, s>>>(src, src, reinterpret_cast<__nv_bfloat16*>(dst_bf16),
+                                                      reinterpret_cast<__nv_bfloat16*>(dst_bf16), nullptr, nullptr, C, HW, 1);
+    CF_CHECK_LAUNCH("prep_transpose_kernel");
     return CF_OK;
 }
 
@@ -480,6 +535,10 @@ int launch_corr_tc2(const void* f1, const void* f2, int in_dtype, int in_layout,
     P.tile_l1 = (can_tile && (tile_knob & 2) && P.level1 && W >= 64 && H % 8 == 0) ? 1 : 0;
     if (tiled_mask) *tiled_mask = (P.tile_l0 ? 1u : 0u) | (P.tile_l1 ? 2u : 0u);
 
+    { const char* e = getenv("CF_TC2_SKIP"); P.skip = e ? atoi(e) : 0; }
+    // operands of the whole batch beyond a third of L2 (re-read by every query block): keep concurrent CTAs on neighbouring pairs
+    P.sched = ((size_t)B * HW * C * 2 * (split ? 2 : 1) > (size_t)40 << 20 && (long)B * P.PB >= 4L * sm_count()) ? 1 : 0;
+    { const char* e = getenv("CF_TC2_SCHED"); if (e) P.sched = atoi(e) != 0; }
     CUtensorMap tmQh, tmQl, tmPh, tmPl;
     const uint64_t rb = (uint64_t)C * 2;     // bytes of one position's channels
     {   // fmap2 as (channels, x, y, batch); box = 8 x of 4 rows

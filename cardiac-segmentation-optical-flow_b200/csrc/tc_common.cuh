@@ -131,6 +131,8 @@ TmapEncodeFn tmap_encode_fn();   // nullptr when the driver does not provide cuT
 // strides_bytes[i] is the stride of dims[i + 1].
 int make_tmap_bf16(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box);
+// one fp32 [B, C, HW] map -> bf16 [B, HW, C] (corr_tc2.cu)
+int launch_prep_transpose_one(const float* src, void* dst_bf16, int B, int C, int HW, cudaStream_t s);
 // multiprocessor count of the current device (cached per device)
 int sm_count();
 // opt a kernel in to `bytes` of dynamic shared memory on the current device, once per (device, slot < 16)

@@ -128,6 +128,19 @@ CF_API int cf_fmap_pyramid_build(const float* f2, int B, int C, int H, int W, in
 CF_API int cf_corr_lookup_fused(const float* f1, const float* f2_pyramid, const float* coords, int B, int C, int H,
                          int W, int L, int r, float* out, void* stream);
 
+/* The same on the tensor cores (tcgen05): the window correlations of a block of 128 queries (an 8 x 16 patch of the fmap) are
+ * one small GEMM per 8 x 16 chunk of the pooled fmap2 covering the block's windows; bf16 operands, fp32 accumulate in TMEM,
+ * bilinear taps with the materialised lookup's exact coordinate arithmetic.  `operands` (cf_corr_otf_operand_bytes, 256-byte
+ * aligned) receives f1 and the pooled f2 levels as bf16 channels-last; `workspace` = cf_fmap_pyramid_bytes(B, C, H, W, L) bytes
+ * of scratch for the fp32 pooled pyramid.  Shapes: H % 8 == 0, W % 16 == 0, C % 8 == 0, C <= 256 (cf_corr_otf_supported);
+ * output within 1e-2 of the fp32 volume's lookup (bf16 operands).  Same contract as corr_fn(coords1), SegFlowGaussian.py:935. */
+CF_API int cf_corr_otf_supported(int B, int C, int H, int W, int L);
+CF_API size_t cf_corr_otf_operand_bytes(int B, int C, int H, int W, int L);
+CF_API int cf_corr_otf_prepare(const float* f1, const float* f2, int B, int C, int H, int W, int L, void* operands,
+                        void* workspace, size_t workspace_bytes, void* stream);
+CF_API int cf_corr_lookup_otf(const void* operands, const float* coords, int B, int C, int H, int W, int L, int r, float* out,
+                       void* stream);
+
 /* ---- a5: SpatialTransformer.forward(flow, original) ----------------------------------------------------------
  * replaces nnunet/network_architecture/integration.py:61-79.  flow [B,2,H,W] (ch0 displaces rows, ch1
  * displaces columns), src [B,C,H,W], out [B,C,H,W]; align_corners=True, zero padding. */

@@ -192,7 +192,8 @@ def test_on_the_fly_lookup_matches_materialised(hw, c, radius, levels):
     f1, f2 = torch.randn(2, c, H, W, generator=g), torch.randn(2, c, H, W, generator=g)
     ref = corr_oracle.CorrBlock(f1, f2, num_levels=levels, radius=radius)
     with torch.no_grad():
-        blk = cf.CorrBlock(f1.to(DEV), f2.to(DEV), num_levels=levels, radius=radius, on_the_fly=True)
+        blk = cf.CorrBlock(f1.to(DEV), f2.to(DEV), num_levels=levels, radius=radius, on_the_fly=True, precision="fp32")
+        assert blk.used_precision == "fp32"       # the CUDA-core variant (the tensor-core one: tests/test_gpu_otf_tc.py)
         for k, sigma in enumerate((0.0, 2.0, 6.0)):
             coords = corr_oracle.coords_grid(2, H, W) + torch.randn(2, 2, H, W, generator=g) * sigma
             if k == 2:

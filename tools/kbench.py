@@ -124,6 +124,21 @@ if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24", "cfg2h", "cfg2q"):
                 blks[i](traj[k], out=outs12[k])
         us, mn = timeit(twelve, nrot, reps=max(5, args.reps // 3))
         report("lookup x12 same pyramid (per call)", us / 12, mn / 12, lb)
+    if want("otf"):     # K4: lookup without a materialised volume -- tensor cores (tcgen05) vs the fp32 CUDA-core variant
+        flops = 0
+        hh, ww = H, W
+        for _ in range(L):
+            flops += 2.0 * C * HWn * min(100, hh * ww)
+            hh, ww = hh // 2, ww // 2
+        flops *= P
+        with torch.no_grad():
+            for prec, label in (("bf16", "tcgen05 bf16"), ("fp32", "CUDA cores fp32")):
+                if prec == "fp32" and args.cfg == "cfg4" and not os.environ.get("KB_OTF_SIMT"):
+                    continue
+                ob = [cf.CorrBlock(f1[i], f2[i], on_the_fly=True, precision=prec) for i in range(nrot)]
+                us, mn = timeit(lambda i: ob[i](coords[i], out=outs[i]), nrot, reps=max(5, args.reps // 3))
+                report(f"on-the-fly lookup [{label}]", us, mn, None, flops)
+                del ob
     if want("pool"):
         us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_pool(pyr[i].data_ptr(), P, H, W, L, 0, _cabi.stream())), nrot)
         lv = [(H >> k) * (W >> k) for k in range(L)]

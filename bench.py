@@ -231,7 +231,11 @@ def run_reference_arm(args, wl):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload + ": " + wl["desc"], "sample": sample_desc},
+        "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step_per_gpu": wl["pairs"], "pairs_timed_per_step": sample,
+                   "corr_precision": "fp32 (torch CPU kernels)", "sample": sample_desc,
+                   "same_config_note": "same workload and metric as the GPU arm; a CPU step times `pairs_timed_per_step` of the "
+                                       "`pairs_per_step_per_gpu` pairs (per-pair cost does not depend on the count) so that the run "
+                                       "ends within minutes; value = pairs timed / time"},
         "cpu_baseline": {"value": value, "unit": "frame-pairs/s", "cores": threads, "kind": "port", "sample": sample_desc},
         "e2e": {"value": value, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -331,11 +335,191 @@ def make_unit_device(wl, seed, dev):
                 label=label)
 
 
-def run_cohort(args, wl):
-    """BASELINE.json configs[4]: the whole synthetic cohort sharded by (patient, slice) over the ranks, no data-path
-    collective, ONE NCCL all_gather of the compact per-unit result rows at the end (cardioflow_b200.shard)."""
+def pin_to_gpu_numa(local_rank):
+    """Bind this rank's host threads to the CPUs NVML reports as local to its GPU BEFORE any pinned buffer is allocated: pinned
+    memory is placed on the NUMA node of the allocating thread, and eight ranks allocating and copying from one socket share
+    that socket's memory controllers and PCIe root complexes (e2e efficiency 0.22 at 8 GPUs)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        try:
+            node = pynvml.nvmlDeviceGetNumaNodeId(h)
+        except Exception:  # noqa: BLE001
+            node = None
+        return {"cpus": len(cpus), "numa_node": node}
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:80]}
+
+
+def cohort_measure(args, wl, dev, rank, world, dist, patients, slices, flow_gather=False):
+    """BASELINE.json configs[4]: the synthetic cohort sharded by (patient, slice) over the ranks, no data-path collective,
+    ONE NCCL all-gather of the per-unit results at the end.  Results of a unit: the registered label maps of its 29 pairs
+    (uint8, written by the mask-warp kernel straight into this rank's slice of the all-gather buffer: the usage pattern of
+    SegFlowGaussian.py:3571-3580 `warp_linear` -> one label map per frame, collected per (patient, slice, frame) like
+    compute_SSIM.py:26-104) plus a compact row (two float64 checksums, four class areas).  Returns the `cohort` object."""
     import cardioflow_b200 as cf
     from cardioflow_b200 import _cabi, shard
+    lib = _cabi.lib()
+    P, H, W, IH, IW = wl["pairs"], wl["H"], wl["W"], wl["IH"], wl["IW"]
+    K81 = LEVELS * (2 * RADIUS + 1) ** 2
+    units = shard.cohort_units(patients, slices)
+    mine = shard.shard_units(units, rank, world)
+    pyramid = torch.empty(lib.cf_corr_pyramid_bytes(P, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
+    outs = torch.empty(ITERS, P, K81, H, W, dtype=torch.float32, device=dev)
+    warped = torch.empty(P, 1, IH, IW, dtype=torch.float32, device=dev)
+    # the pairs of a unit are independent: n parallel chains over contiguous sub-batches (cardioflow_b200.Lanes)
+    bounds = cf.lane_bounds(P, max(1, args.lanes))
+    lanes = cf.Lanes(len(bounds), dev)
+    lane_pyr = ([torch.empty(lib.cf_corr_pyramid_bytes(b - a, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
+                 for a, b in bounds] if len(bounds) > 1 else [pyramid])
+    lane_counts = torch.zeros(len(bounds), 4, dtype=torch.int64, device=dev)
+    sum_ws = torch.empty(lib.cf_sum_f64_workspace_bytes() // 8, dtype=torch.float64, device=dev)
+    # result buffers: allocated as the RECEIVE buffers of the final all-gather; kernels write into this rank's slice
+    maps = shard.GatherBuffer(len(units), (P, 1, IH, IW), torch.uint8, dev, rank=rank, world_size=world)
+    sums = shard.GatherBuffer(len(units), (2,), torch.float64, dev, rank=rank, world_size=world)
+    areas = shard.GatherBuffer(len(units), (len(bounds), 4), torch.int64, dev, rank=rank, world_size=world)
+    lab_scratch = torch.empty(P, 1, IH, IW, dtype=torch.uint8, device=dev)
+    sum_scratch = torch.zeros(2, dtype=torch.float64, device=dev)
+    area_scratch = torch.zeros(len(bounds), 4, dtype=torch.int64, device=dev)
+
+    def chain(u, j, a, b, lab_out, area_out):
+        blk = cf.CorrBlock(u["f1"][a:b], u["f2"][a:b], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                           pyramid_buffer=lane_pyr[j])
+        for k in range(ITERS):
+            blk(u["coords"][k, a:b], out=outs[k, a:b])
+        cf.warp(u["img"][a:b], u["flow"][a:b], out=warped[a:b])
+        # registered label maps (uint8) + the lane's class areas, from ONE launch, straight into the result buffers
+        cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4, out=lab_out[a:b], return_counts=True,
+                              counts_out=area_out[j], counts_total=True)
+        return blk
+
+    def compute(u, lab_out, sum_out, area_out):
+        lanes.run(P, lambda j, a, b: chain(u, j, a, b, lab_out, area_out))
+        shard.sum_f64(outs[ITERS - 1], sum_out[0:1], sum_ws)     # one pass, fixed summation order (cf_sum_f64)
+        shard.sum_f64(warped, sum_out[1:2], sum_ws)
+
+    with torch.no_grad():
+        # static input / output buffers + ONE CUDA graph of a unit's whole device work (replayed per unit); the results of a
+        # replay land in fixed staging slices only because a graph bakes addresses in: one device copy per unit moves them
+        # into the unit's slot (the eager path, --no-graph, writes the slots directly)
+        static = make_unit_device(wl, shard.unit_seed(*units[0]), dev)
+        g_lab = torch.empty(P, 1, IH, IW, dtype=torch.uint8, device=dev)
+        g_sum = torch.zeros(2, dtype=torch.float64, device=dev)
+        g_area = torch.zeros(len(bounds), 4, dtype=torch.int64, device=dev)
+        compute(static, g_lab, g_sum, g_area)
+        torch.cuda.synchronize()
+        graph = None
+        if not args.no_graph:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                compute(static, g_lab, g_sum, g_area)
+
+        def run_unit(seed, lab_dst, sum_dst, area_dst):
+            u = make_unit_device(wl, seed, dev)              # input synthesis: not part of the path, not timed
+            for k, v in u.items():
+                static[k].copy_(v)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if graph:
+                graph.replay()
+                lab_dst.copy_(g_lab)
+                sum_dst.copy_(g_sum)
+                area_dst.copy_(g_area)
+            else:
+                compute(static, lab_dst, sum_dst, area_dst)
+            e1.record()
+            return e0, e1
+
+        for _ in range(max(args.warmup, 3)):
+            run_unit(shard.unit_seed(*units[0]), lab_scratch, sum_scratch, area_scratch)
+        if dist:                                             # communicator set-up is not part of the gather being timed
+            warm = torch.zeros(world, 4, dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(warm.view(-1), warm[rank].reshape(-1))
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        sampler = ClockSampler(dev.index)
+        sampler.start()
+        evs = [run_unit(shard.unit_seed(pat, sl), maps.local[i], sums.local[i], areas.local[i]) for i, (pat, sl) in enumerate(mine)]
+        # The per-unit intervals exclude the (untimed) input synthesis between units, whose wall-clock cost differs from rank
+        # to rank; without a barrier here that skew would be charged to the gather as waiting time.  Compute skew is already
+        # in the max over ranks of compute_ms; the gather is timed from a common start.
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        t_maps, t_sums, t_areas = maps.gather(), sums.gather(), areas.gather()      # in place: send buffer = recv[rank]
+        g1.record()
+        torch.cuda.synchronize()
+        clocks = sampler.stop()
+        compute_ms = sum(a.elapsed_time(b) for a, b in evs)
+        gather_ms = g0.elapsed_time(g1)
+        # the gathered results must equal what any rank computes for a unit on its own (deterministic kernels)
+        check = []
+        if rank == 0:
+            for j in sorted({0, len(units) // 2, len(units) - 1, min(1, len(units) - 1)}):
+                run_unit(shard.unit_seed(*units[j]), lab_scratch, sum_scratch, area_scratch)
+                check.append(bool(torch.equal(lab_scratch, maps.unit(t_maps, j)) and torch.equal(sum_scratch, sums.unit(t_sums, j))
+                                  and torch.equal(area_scratch, areas.unit(t_areas, j))
+                                  and int(area_scratch.sum()) == P * IH * IW))
+            torch.cuda.synchronize()
+        # optional: the worst-case payload of SURVEY 8(e), the full-resolution flows (2 x 256^2 x 4 B per pair)
+        flow_info = None
+        if flow_gather and dist:
+            fbuf = shard.GatherBuffer(len(units), (P, 2, IH, IW), torch.float32, dev, rank=rank, world_size=world)
+            for i in range(len(mine)):
+                fbuf.local[i].copy_(static["flow"])           # stand-in payload: the flows are the network's output, not this path's
+            torch.cuda.synchronize()
+            dist.barrier()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            fbuf.gather()
+            f1.record()
+            torch.cuda.synchronize()
+            flow_info = [f0.elapsed_time(f1), fbuf.nbytes_sent]
+            del fbuf
+    t = torch.tensor([compute_ms, gather_ms, flow_info[0] if flow_info else 0.0], dtype=torch.float64, device=dev)
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    compute_ms, gather_ms, flow_ms = t.tolist()
+    total_ms = compute_ms + gather_ms            # slowest rank's compute, then the gather from the common barrier
+    n_pairs = len(units) * P
+    payload = maps.nbytes_sent + sums.nbytes_sent + areas.nbytes_sent
+    out = {
+        "workload": "cfg5: " + WORKLOADS["cfg5"]["desc"], "scaling": "strong", "value": n_pairs / (total_ms * 1e-3),
+        "unit": "frame-pairs/s", "patients": patients, "slices": slices, "units": len(units), "units_on_rank0": len(mine),
+        "pairs_per_unit": P, "lanes": len(bounds), "corr_precision": args.precision,
+        "compute_ms_max_rank": compute_ms, "gather_ms_max_rank": gather_ms, "clocks": clocks,
+        "launch": "eager launches from Python, one unit at a time" if args.no_graph else
+                  "one CUDA graph replay per unit (build + 12 lookups + warp + uint8 mask warp with class areas + 2 checksums)",
+        "timing": "value = pairs / (max over ranks of the summed per-unit device intervals + max over ranks of the gather timed from a barrier)",
+        "gather": {"collective": "all_gather_into_tensor (NCCL, in place: send buffer = this rank's slice of the receive buffer)"
+                                 if world > 1 else "none (1 rank)",
+                   "payload": "registered label maps uint8 [units, 29, 1, 256, 256] + 2 float64 checksums + class areas per unit",
+                   "bytes_sent_per_rank": int(payload), "bytes_total": int(payload * world),
+                   "gbytes_per_s_per_rank_received": (payload * (world - 1) / (gather_ms * 1e-3) / 1e9) if world > 1 and gather_ms > 0 else None,
+                   "units_verified_on_rank0": check},
+        "gpu_launches": len(mine) * ((2 + ITERS + 2) * len(bounds) + 4 + (3 if graph else 0)),
+    }
+    if flow_info:
+        out["flow_gather_variant"] = {"what": "SURVEY 8(e) worst case: full-resolution flows fp32 [units, 29, 2, 256, 256] through the same in-place all-gather",
+                                      "bytes_sent_per_rank": int(flow_info[1]), "bytes_total": int(flow_info[1] * world), "ms_max_rank": flow_ms,
+                                      "gbytes_per_s_per_rank_received": flow_info[1] * (world - 1) / (flow_ms * 1e-3) / 1e9 if flow_ms > 0 else None}
+    if rank == 0 and not all(check):
+        out["error"] = "gathered results differ from a local recomputation"
+    return out
+
+
+def run_cohort(args, wl):
+    """`--workload cfg5`: the cohort alone (the default run attaches the same object as `cohort` when N > 1)."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -347,124 +531,21 @@ def run_cohort(args, wl):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    lib = _cabi.lib()
-    P, H, W, IH, IW = wl["pairs"], wl["H"], wl["W"], wl["IH"], wl["IW"]
-    K81 = LEVELS * (2 * RADIUS + 1) ** 2
-    units = shard.cohort_units(args.patients, args.slices)
-    mine = shard.shard_units(units, rank, world)
-    pyramid = torch.empty(lib.cf_corr_pyramid_bytes(P, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
-    outs = torch.empty(ITERS, P, K81, H, W, dtype=torch.float32, device=dev)
-    warped = torch.empty(P, 1, IH, IW, dtype=torch.float32, device=dev)
-    WIDTH = 6   # row: [checksum of the last lookup, sum of the warped frames, 4 warped-label pixel counts]
-
-    # the pairs of a unit are independent: n parallel chains over contiguous sub-batches (cardioflow_b200.Lanes)
-    bounds = cf.lane_bounds(P, max(1, args.lanes))
-    lanes = cf.Lanes(len(bounds), dev)
-    lane_pyr = ([torch.empty(lib.cf_corr_pyramid_bytes(b - a, H, W, LEVELS) // 4, dtype=torch.float32, device=dev)
-                 for a, b in bounds] if len(bounds) > 1 else [pyramid])
-    lab = torch.empty(P, 1, IH, IW, dtype=torch.int64, device=dev)
-    frame_counts = torch.zeros(P, 4, dtype=torch.int64, device=dev)
-    sum_ws = torch.empty(lib.cf_sum_f64_workspace_bytes() // 8, dtype=torch.float64, device=dev)
-
-    def chain(u, j, a, b):
-        blk = cf.CorrBlock(u["f1"][a:b], u["f2"][a:b], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
-                           pyramid_buffer=lane_pyr[j])
-        for k in range(ITERS):
-            blk(u["coords"][k, a:b], out=outs[k, a:b])
-        cf.warp(u["img"][a:b], u["flow"][a:b], out=warped[a:b])
-        cf.warp_onehot_argmax(u["flow"][a:b], u["label"][a:b], num_classes=4, out=lab[a:b], return_counts=True,
-                              counts_out=frame_counts[a:b])   # per-frame class areas, straight into the unit's table
-        return blk
-
-    def compute(u, row):
-        lanes.run(P, lambda j, a, b: chain(u, j, a, b))
-        shard.sum_f64(outs[ITERS - 1], row[0:1], sum_ws)     # one pass, fixed summation order (cf_sum_f64)
-        shard.sum_f64(warped, row[1:2], sum_ws)
-        torch.sum(frame_counts, dim=0, dtype=torch.float64, out=row[2:6])   # warped-label pixel counts (from the mask warp launch)
-
-    with torch.no_grad():
-        rows = torch.zeros(max(len(mine), 1), WIDTH, dtype=torch.float64, device=dev)
-        # static input buffers + ONE CUDA graph of a unit's whole device work (replayed per unit)
-        static = make_unit_device(wl, shard.unit_seed(*units[0]), dev)
-        row_buf = torch.zeros(WIDTH, dtype=torch.float64, device=dev)
-        compute(static, row_buf)
-        torch.cuda.synchronize()
-        graph = None
-        if not args.no_graph:
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                compute(static, row_buf)
-
-        def run_unit(seed, dst):
-            u = make_unit_device(wl, seed, dev)              # input synthesis: not part of the path, not timed
-            for k, v in u.items():
-                static[k].copy_(v)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            if graph:
-                graph.replay()
-            else:
-                compute(static, row_buf)
-            dst.copy_(row_buf)
-            e1.record()
-            return e0, e1
-
-        scratch = torch.zeros(WIDTH, dtype=torch.float64, device=dev)
-        for _ in range(max(args.warmup, 3)):
-            run_unit(shard.unit_seed(*units[0]), scratch)
-        if dist:                                             # communicator set-up is not part of the gather being timed
-            shard.gather_results(rows[:len(mine)], len(units), rank=rank, world_size=world)
-        torch.cuda.synchronize()
-        if dist:
-            dist.barrier()
-        sampler = ClockSampler(local_rank)
-        sampler.start()
-        evs = [run_unit(shard.unit_seed(pat, sl), rows[i]) for i, (pat, sl) in enumerate(mine)]
-        # The per-unit intervals exclude the (untimed) input synthesis between units, whose wall-clock cost differs from rank
-        # to rank; without a barrier here that skew would be charged to the gather as waiting time.  Compute skew is already
-        # in the max over ranks of compute_ms; the gather is timed from a common start.
-        torch.cuda.synchronize()
-        if dist:
-            dist.barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        table = shard.gather_results(rows[:len(mine)], len(units), rank=rank, world_size=world)
-        g1.record()
-        torch.cuda.synchronize()
-        clocks = sampler.stop()
-        compute_ms = sum(a.elapsed_time(b) for a, b in evs)
-        gather_ms = g0.elapsed_time(g1)
-        # the gathered table must equal what any rank computes for a unit on its own (deterministic kernels)
-        check = []
-        if rank == 0:
-            for j in sorted({0, len(units) // 2, len(units) - 1, min(1, len(units) - 1)}):
-                run_unit(shard.unit_seed(*units[j]), scratch)
-                check.append(bool(torch.equal(scratch, table[j])))
-            torch.cuda.synchronize()
-    t = torch.tensor([compute_ms, gather_ms], dtype=torch.float64, device=dev)
-    if dist:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    compute_ms, gather_ms = t.tolist()
-    total_ms = compute_ms + gather_ms            # slowest rank's compute, then the gather from the common barrier
+    co = cohort_measure(args, wl, dev, rank, world, dist, args.patients, args.slices, flow_gather=args.flow_gather)
     if rank == 0:
-        n_pairs = len(units) * P
-        line = {
-            "metric": METRIC, "value": n_pairs / (total_ms * 1e-3), "unit": "frame-pairs/s", "n_gpus": world,
-            "steps": len(units), "warmup": max(args.warmup, 3), "ms_per_step": total_ms / max(len(mine), 1),
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "bf16 GEMM (fp32 accumulate) / f32 lookup+warp", "data": "synthetic",
-            "config": {"workload": "cfg5: " + wl["desc"], "patients": args.patients, "slices": args.slices,
-                       "units": len(units), "units_on_rank0": len(mine), "pairs_per_unit": P, "lanes": len(bounds),
-                       "launch": "eager launches from Python, one unit at a time" if args.no_graph else "one CUDA graph replay per unit (build + 12 lookups + warp + mask warp + result row)",
-                       "l2": "every unit has fresh inputs and writes 623 MB (> 126 MB L2)"},
-            "clocks": clocks, "compute_ms_max_rank": compute_ms, "gather_ms_max_rank": gather_ms,
-            "timing": "value = pairs / (max over ranks of the summed per-unit device intervals + max over ranks of the gather timed from a barrier)",
-            "gather": {"collective": "all_gather_into_tensor (NCCL)" if world > 1 else "none (1 rank)",
-                       "bytes_per_rank": int(rows[:len(mine)].numel() * 8), "rows_verified_on_rank0": check},
-            "gpu_launches": len(mine) * ((2 + ITERS + 2) * len(bounds) + 4),   # + two cf_sum_f64 (2 launches each)
-        }
-        if not all(check):
-            line["error"] = "gathered rows differ from a local recomputation"
+        line = {"metric": METRIC, "value": co["value"], "unit": "frame-pairs/s", "n_gpus": world, "steps": co["units"],
+                "warmup": max(args.warmup, 3), "ms_per_step": (co["compute_ms_max_rank"] + co["gather_ms_max_rank"]) / max(co["units_on_rank0"], 1),
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "bf16 GEMM (fp32 accumulate) / f32 lookup+warp" if args.precision == "bf16" else "f32-grade GEMM / f32 lookup+warp",
+                "data": "synthetic",
+                "config": {k: co[k] for k in ("workload", "patients", "slices", "units", "units_on_rank0", "pairs_per_unit", "lanes", "launch", "corr_precision")},
+                "clocks": co["clocks"], "compute_ms_max_rank": co["compute_ms_max_rank"], "gather_ms_max_rank": co["gather_ms_max_rank"],
+                "timing": co["timing"], "gather": co["gather"], "gpu_launches": co["gpu_launches"]}
+        line["config"]["l2"] = "every unit has fresh inputs and writes 623 MB (> 126 MB L2)"
+        if "flow_gather_variant" in co:
+            line["flow_gather_variant"] = co["flow_gather_variant"]
+        if "error" in co:
+            line["error"] = co["error"]
         emit(line)
     if dist:
         dist.destroy_process_group()
@@ -583,8 +664,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "bf16x3", "fp32"],
-                    help="correlation build: auto = fp32-grade like the reference (bf16x3 split on tcgen05, else fp32 CUDA cores); bf16 is opt-in")
+    ap.add_argument("--precision", default="bf16", choices=["auto", "bf16", "bf16x3", "fp32"],
+                    help="correlation build.  The library default (auto) is fp32-grade like the reference (bf16x3 split on tcgen05); the "
+                         "bench headline uses plain bf16 operands, the tolerance north_star states for the tensor-core correlation "
+                         "(<= 1e-2 relative, fp32 accumulate); both are reported in profiles/")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from Python instead of replaying one CUDA graph per step")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -596,6 +679,11 @@ def main():
                          "1 = one chain over the whole batch")
     ap.add_argument("--patients", type=int, default=150, help="cfg5 only")
     ap.add_argument("--slices", type=int, default=10, help="cfg5 only")
+    ap.add_argument("--flow-gather", action="store_true", help="cfg5 / cohort: also time the all-gather of the full-resolution flows (22.8 GB in all)")
+    ap.add_argument("--cohort-patients", type=int, default=150,
+                    help="N > 1: size of the cfg5 cohort run after the main measurement and reported as `cohort` (0 = skip)")
+    ap.add_argument("--on-the-fly", action="store_true",
+                    help="cfg2 / cfg4: CorrBlock(on_the_fly=True): no materialised volume, window correlations recomputed per lookup on tcgen05")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -626,6 +714,11 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     _cabi.lib()  # fail loudly if the extension is missing
+    affinity = pin_to_gpu_numa(local_rank)      # before the first pinned allocation
+    if args.on_the_fly:
+        if args.workload not in ("cfg2", "cfg4"):
+            sys.exit("--on-the-fly applies to cfg2 / cfg4")
+        args.lanes = 1                          # the on-the-fly kernel is persistent over the whole batch
     if args.l2_persist_mb:
         import ctypes
         rt = ctypes.CDLL("libcudart.so.12")
@@ -648,8 +741,12 @@ def main():
     ev_l1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
 
     def step(u, ev=None):
-        blk = cf.CorrBlock(u["f1"], u["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
-                           pyramid_buffer=pyramid)
+        if args.on_the_fly:
+            blk = cf.CorrBlock(u["f1"], u["f2"], num_levels=LEVELS, radius=RADIUS, on_the_fly=True,
+                               precision="fp32" if args.precision == "fp32" else "bf16")
+        else:
+            blk = cf.CorrBlock(u["f1"], u["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                               pyramid_buffer=pyramid)
         if ev:
             ev[0].record()
         for k in range(ITERS):
@@ -688,6 +785,7 @@ def main():
         torch.cuda.synchronize()
         use_graph = not args.no_graph
         graphs = lookup_graphs = full_graphs = None
+        lane_lookup_graphs = []
         if n_lanes > 1:
             step_lanes(sets[0])
             torch.cuda.synchronize()
@@ -712,6 +810,12 @@ def main():
                 with torch.cuda.graph(gph):
                     lookups_only(u, bk)
                 lookup_graphs.append(gph)
+            if n_lanes > 1:                        # ... and as the step runs them: one 12-lookup chain per lane, concurrently
+                for u, lane_blks in zip(sets, keep):
+                    gph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gph):
+                        lanes.run(P, lambda j, a, b, u=u, lb=lane_blks: [lb[j](u["coords"][k, a:b], out=outs[k, a:b]) for k in range(ITERS)])
+                    lane_lookup_graphs.append(gph)
 
         def run_step(i):
             if graphs:
@@ -754,6 +858,17 @@ def main():
                 step(sets[i % n_sets], (ev_l0[i], ev_l1[i]))
         torch.cuda.synchronize()
         lookup_ms = sorted(ev_l0[i].elapsed_time(ev_l1[i]) for i in range(n_ev))[n_ev // 2] / ITERS
+        # the same 12 lookups in the configuration of the step: each lane's chain on its own stream, all lanes at once
+        lane_lookup_ms = None
+        if lane_lookup_graphs:
+            evs2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_ev)]
+            for i in range(n_ev):
+                graphs[i % n_sets].replay()
+                evs2[i][0].record()
+                lane_lookup_graphs[i % n_sets].replay()
+                evs2[i][1].record()
+            torch.cuda.synchronize()
+            lane_lookup_ms = sorted(a.elapsed_time(b) for a, b in evs2)[n_ev // 2] / ITERS
 
         # ---- end-to-end leg: pinned host buffers -> public module API -> pinned host results ----
         e2e_steps = args.e2e_steps or min(args.steps, 10)
@@ -785,8 +900,12 @@ def main():
                 upload(i + 1)
             main_stream.wait_event(in_ready[s])
             d = dbuf[s]
-            b = cf.CorrBlock(d["f1"], d["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
-                             pyramid_buffer=pyramid)
+            if args.on_the_fly:
+                b = cf.CorrBlock(d["f1"], d["f2"], num_levels=LEVELS, radius=RADIUS, on_the_fly=True,
+                                 precision="fp32" if args.precision == "fp32" else "bf16")
+            else:
+                b = cf.CorrBlock(d["f1"], d["f2"], num_levels=LEVELS, radius=RADIUS, precision=args.precision,
+                                 pyramid_buffer=pyramid)
             for k in range(ITERS):
                 b(d["coords"][k], out=outs[k])
                 h_outs[k].copy_(outs[k], non_blocking=True)
@@ -814,9 +933,10 @@ def main():
         e2e_ms = e0.elapsed_time(e1)
 
     if dist:
-        t = torch.tensor([ms_total, e2e_ms, lookup_ms], dtype=torch.float64, device=dev)
+        t = torch.tensor([ms_total, e2e_ms, lookup_ms, lane_lookup_ms or 0.0], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, e2e_ms, lookup_ms = t.tolist()
+        ms_total, e2e_ms, lookup_ms, lane_lookup_ms = t.tolist()
+        lane_lookup_ms = lane_lookup_ms or None
     value = world * P * args.steps / (ms_total * 1e-3)
     e2e_value = world * P * e2e_steps / (e2e_ms * 1e-3)
 
@@ -840,9 +960,12 @@ def main():
         build_launches = 1 + (LEVELS - 1)
     else:
         # version 2 of the build (H % 4 == 0, W % 8 == 0): pre-pass + persistent GEMM (levels 0-2) + one pool launch per further level
-        v2 = H % 4 == 0 and W % 8 == 0
+        # plain bf16 at W = 32: version 1 (pre-pass + GEMM writing all four levels); else version 2
+        v2 = H % 4 == 0 and W % 8 == 0 and not (used_precision == "bf16" and W == 32)
         build_launches = (2 + max(0, LEVELS - 3)) if v2 else 2 + (0 if (W == 32 and LEVELS <= 4) else LEVELS - 2)
     launches_per_step = (build_launches + ITERS + 1) * n_lanes
+    if args.on_the_fly:                          # pooled fmap2 pyramid (copy + 3 pools) + 5 transposes, 12 lookups, 1 warp
+        launches_per_step = (1 + (LEVELS - 1) + 1 + LEVELS) + ITERS + 1
 
     line = {
         "metric": METRIC, "value": value, "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
@@ -868,6 +991,42 @@ def main():
                      "launch_timed": f"all {P} pairs in one launch, alone on its stream",
                      "frac_of_nominal_8000": achieved / 8000.0},
     }
+    line["config"]["host_affinity"] = affinity
+    if lane_lookup_ms:
+        # informational: the same kernel as the step runs it (one chain per lane, lanes concurrent): bytes of the whole batch over the
+        # elapsed time per lookup iteration.  `frac` above stays the conservative single-launch figure.
+        line["roofline"]["as_run_in_the_step"] = {
+            "what": f"{n_lanes} lanes x 12 lookups as parallel stream branches (the step's configuration), elapsed / 12",
+            "ms_per_lookup_iteration": lane_lookup_ms, "achieved": lookup_bytes / (lane_lookup_ms * 1e-3) / 1e9,
+            "frac": lookup_bytes / (lane_lookup_ms * 1e-3) / 1e9 / peak}
+    if args.on_the_fly:
+        # K4: the dominant kernel is the tensor-core lookup; useful work = SURVEY 8(d) K4 (window products a per-query kernel needs;
+        # the bounding-box GEMMs execute several times that)
+        flops, hh, ww = 0.0, H, W
+        for _ in range(LEVELS):
+            flops += 2.0 * C * H * W * min(100, hh * ww)
+            hh, ww = hh // 2, ww // 2
+        flops *= P
+        tpeak = 1365.0
+        if os.path.exists(peaks_path):
+            with open(peaks_path) as f:
+                tpeak = json.load(f).get("bf16_tflops_sustained", tpeak)
+        op_bytes = lib.cf_corr_otf_operand_bytes(P, C, H, W, LEVELS)
+        line["config"]["on_the_fly"] = {"operand_bytes": int(op_bytes), "materialised_pyramid_bytes": int(pyr_floats * 4),
+                                        "variant": "tcgen05 (bf16 operands, fp32 accumulate)" if used_precision == "bf16" else "CUDA cores fp32"}
+        line["roofline"] = {"kernel": "lookup_tc_kernel<4>", "bound": "tensor", "achieved": flops / (lookup_ms * 1e-3) / 1e12, "peak": tpeak,
+                            "unit": "TFLOP/s", "frac": flops / (lookup_ms * 1e-3) / 1e12 / tpeak, "traffic": None,
+                            "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained",
+                            "useful_flops_per_launch": flops, "avg_launch_ms": lookup_ms,
+                            "note": "useful FLOPs = sum_l 2*C*HW*min(100, h_l*w_l) per pair (SURVEY 8(d) K4); the kernel is bound by L2 operand "
+                                    "streaming and its epilogue, not by the tensor pipe (DESIGN section 8)",
+                            "output_bytes_per_launch": 4 * P * K81 * H * W,
+                            "output_gbytes_per_s": 4 * P * K81 * H * W / (lookup_ms * 1e-3) / 1e9}
+    # ---- N > 1: the path's real multi-GPU design (cfg5 cohort, strong scaling, one NCCL all-gather of the label maps) ----
+    if world > 1 and args.cohort_patients > 0 and not args.on_the_fly:
+        line_cohort = cohort_measure(args, WORKLOADS["cfg5"], dev, rank, world, dist, args.cohort_patients, args.slices,
+                                     flow_gather=True)
+        line["cohort"] = line_cohort
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sample = 1 if args.workload == "cfg4" else 4
         v, cores, reps = cpu_pairs_per_sec(wl, sample)

@@ -47,6 +47,7 @@ _SIGNATURES = {
     "cf_warp2d_taps": (_I, [_P, _I, _I, _I, _P, _P]),
     "cf_warp2d_onehot_argmax": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "cf_warp2d_onehot_argmax_counts": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_warp2d_onehot_argmax_u8": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _I, _P]),
     "cf_warp2d_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_warp2d_nearest_bwd": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "cf_corr_lookup_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),

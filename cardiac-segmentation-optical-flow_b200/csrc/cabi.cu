@@ -1,5 +1,6 @@
 // extern "C" entry points of libcardioflow.so (include/cardioflow.h): argument validation + dispatch.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -133,7 +134,13 @@ int cf_corr_build_ex(const void* f1, const void* f2, int in_dtype, int in_layout
     int used = CF_PREC_FP32;
     if (precision != CF_PREC_FP32) {
         const bool want_split = precision != CF_PREC_BF16;
-        if (corr_tc2_supported(B, C, H, W) && aligned16(f1) && aligned16(f2)) {
+        // plain bf16 at W = 32 (the cfg2 / cfg5 shape): version 1's register-resident epilogue pools inside a thread and is the
+        // faster builder there (71 vs 76 us at cfg2); version 2 serves the fp32-grade split mode, every other width (tiled
+        // levels 0 / 1) and non-fp32-NCHW inputs.  CF_BF16_W32_V1=0 forces version 2 (A/B knob).
+        static const bool v1_knob = [] { const char* e = getenv("CF_BF16_W32_V1"); return e ? atoi(e) != 0 : true; }();
+        const bool prefer_v1 = v1_knob && !want_split && plain && W == 32 && H % 4 == 0 && corr_tcgen05_supported(B, C, H, W, true) &&
+                               aligned16(f1) && aligned16(f2);
+        if (!prefer_v1 && corr_tc2_supported(B, C, H, W) && aligned16(f1) && aligned16(f2)) {
             int done = 1;
             rc = launch_corr_tc2(f1, f2, in_dtype, in_layout, B, C, H, W, levels, L, want_split, workspace, workspace_bytes, &done,
                                  (flags & CF_BUILD_ALLOW_TILED) != 0, tiled_mask, s);
@@ -228,6 +235,13 @@ int cf_warp2d_onehot_argmax_counts(const float* flow, const int64_t* label, int 
     CF_REQUIRE(B > 0 && H > 1 && W > 1 && num_classes > 0, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_counts: bad shape");
     CF_REQUIRE(out != label, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_counts: out must not alias label");
     return launch_warp2d_onehot_argmax(flow, label, num_classes, B, H, W, out, counts, (cudaStream_t)stream);
+}
+
+int cf_warp2d_onehot_argmax_u8(const float* flow, const int64_t* label, int num_classes, int B, int H, int W, uint8_t* out,
+                               int64_t* counts, int counts_total, void* stream) {
+    CF_REQUIRE(flow && label && out, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_u8: null pointer");
+    CF_REQUIRE(B > 0 && H > 1 && W > 1 && num_classes > 0, CF_ERR_BAD_ARG, "cf_warp2d_onehot_argmax_u8: bad shape");
+    return launch_warp2d_onehot_argmax_u8(flow, label, num_classes, B, H, W, out, counts, counts_total != 0, (cudaStream_t)stream);
 }
 
 // ---- on-the-fly lookup (K4) --------------------------------------------------------------------------------

@@ -88,6 +88,8 @@ int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int 
 int launch_warp2d_taps(const float* flow, int B, int H, int W, float* taps, cudaStream_t s);
 int launch_warp2d_onehot_argmax(const float* flow, const int64_t* label, int ncls, int B, int H, int W,
                                 int64_t* out, int64_t* counts, cudaStream_t s);   // counts: nullptr or [B, ncls]
+int launch_warp2d_onehot_argmax_u8(const float* flow, const int64_t* label, int ncls, int B, int H, int W, uint8_t* out,
+                                   int64_t* counts, int counts_total, cudaStream_t s);   // counts: nullptr, [B, ncls] or (total) [ncls]
 int launch_warp2d_bwd(const float* flow, const float* src, const float* go, int B, int C, int H, int W,
                       float* gsrc, float* gflow, cudaStream_t s);
 int launch_warp2d_nearest_bwd(const float* flow, const float* go, int B, int C, int H, int W, float* gsrc, cudaStream_t s);

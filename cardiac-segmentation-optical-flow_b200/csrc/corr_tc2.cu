@@ -105,7 +105,7 @@ constexpr uint32_t OP_BYTES = 128u * 128u;   // one 128-row x 64-channel bf16 op
 
 template <bool SPLIT> struct Cfg {
     static constexpr int PARTS = SPLIT ? 2 : 1;          // hi (+ lo)
-    static constexpr int NSTAGE = SPLIT ? 3 : 5;
+    static constexpr int NSTAGE = SPLIT ? 3 : 6;           // (9 stages measured no faster than 5: the kernel is L2-throughput bound)
     static constexpr uint32_t STAGE_BYTES = OP_BYTES * PARTS;
     static constexpr size_t smem_bytes(int k_blocks) {
         return 1024 + (size_t)k_blocks * OP_BYTES * PARTS + (size_t)NSTAGE * STAGE_BYTES + 256;
@@ -153,14 +153,17 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
     //   sched 0: a contiguous 1/gridDim share of all units (equal shares; a CTA reloads its query block 2-3 times);
     //   sched 1: whole keys dealt round-robin -- at any time the CTAs work on neighbouring keys, i.e. on a few pairs, so the
     //            fmap2 operand they all re-read stays in L2 when the batch's operands exceed it (cfg4: 134 MB).
-    const long u_begin = P.units * (long)blockIdx.x / (long)gridDim.x;
-    const long n_keys = (long)P.B * P.PB;
-    const long n_it = P.sched == 0 ? P.units * ((long)blockIdx.x + 1) / (long)gridDim.x - u_begin
-                                   : ((n_keys - (long)blockIdx.x + (long)gridDim.x - 1) / (long)gridDim.x) * P.QT;
-    auto unit_at = [&](long it, long& key, int& qt) {
-        if (P.sched == 0) { const long u = u_begin + it; key = u / P.QT; qt = (int)(u - key * P.QT); }
-        else { const long kq = it / P.QT; key = (long)blockIdx.x + kq * (long)gridDim.x; qt = (int)(it - kq * P.QT); }
+    // 32-bit arithmetic (the host checks units < 2^31) and incremental stepping: no division per tile.
+    const int G = (int)gridDim.x, bid = (int)blockIdx.x;
+    const int n_keys = P.B * P.PB;
+    const int u_begin = (int)((long)P.units * bid / G);
+    const int n_it = P.sched == 0 ? (int)((long)P.units * (bid + 1) / G) - u_begin : ((n_keys - bid + G - 1) / G) * P.QT;
+    struct UnitIter {
+        int key, qt, step, QT;
+        __device__ __forceinline__ void next() { if (++qt == QT) { qt = 0; key += step; } }
+        __device__ __forceinline__ int next_key() const { return qt + 1 == QT ? key + step : key; }
     };
+    const UnitIter it0 = P.sched == 0 ? UnitIter{u_begin / P.QT, u_begin % P.QT, 1, P.QT} : UnitIter{bid, 0, G, P.QT};
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NSTAGE; ++s) { mbar_init(bar(kFull + s), 1); mbar_init(bar(kEmpty + s), 1); }
@@ -182,13 +185,13 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
         // ===================== TMA producer =====================
         if (lane == 0) {
             int stage = 0, phase = 0, n_res = 0;
-            long cur_key = -1;
-            for (long it = 0; it < n_it; ++it) {
-                long key;                                  // b * PB + pb
-                int qt;
-                unit_at(it, key, qt);
-                const int pb = (int)(key % P.PB), b = (int)(key / P.PB);
+            int cur_key = -1, pb = 0, b = 0;
+            UnitIter it = it0;
+            for (int n = 0; n < n_it; ++n, it.next()) {
+                const int key = it.key, qt = it.qt;        // key = b * PB + pb
                 if (key != cur_key) {
+                    b = key / P.PB;
+                    pb = key - b * P.PB;
                     // the MMAs of the previous query block must have retired before its operand is overwritten
                     if (n_res > 0) mbar_wait(bar(kPEmpty), (uint32_t)((n_res - 1) & 1));
                     mbar_expect_tx(bar(kPFull), (uint32_t)P.k_blocks * OP_BYTES * K::PARTS);
@@ -205,10 +208,6 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
                     mbar_expect_tx(bar(kFull + stage), K::STAGE_BYTES);
                     // four boxes (64 channels, 8 x, 4 y) = 32 rows = 4 KB each: smem row = 32 * x-block + 8 * y + x (= TMEM lane);
                     // x-blocks beyond the map are zero-filled
-                    if (P.skip & 8) {     // timing experiment: ONE 3-D box of 128 consecutive positions (results are wrong)
-                        tma_load_3d(ring(stage, 0), &tmPh, bar(kFull + stage), kb * BK, qt * 128, b);
-                        if (SPLIT) tma_load_3d(ring(stage, 1), &tmPl, bar(kFull + stage), kb * BK, qt * 128, b);
-                    } else
 #pragma unroll
                     for (int xb = 0; xb < 4; ++xb) {
                         tma_load_4d(ring(stage, 0) + (uint32_t)xb * 4096u, &tmQh, bar(kFull + stage), kb * BK, 32 * tx + 8 * xb, 4 * ty, b);
@@ -224,12 +223,11 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
         if (lane == 0) {
             const uint32_t idesc = umma_idesc(TQ, NP);
             int stage = 0, phase = 0, n_res = 0;
-            long cur_key = -1;
-            long t = 0;
-            for (long it = 0; it < n_it; ++it, ++t) {
-                long key;
-                int qt_unused;
-                unit_at(it, key, qt_unused);
+            int cur_key = -1;
+            int t = 0;
+            UnitIter it = it0;
+            for (int n = 0; n < n_it; ++n, ++t, it.next()) {
+                const int key = it.key;
                 if (key != cur_key) {
                     mbar_wait(bar(kPFull), (uint32_t)(n_res & 1));
                     ++n_res;
@@ -258,9 +256,7 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
                     if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(bar(kAccFull + acc));
-                long next_key = -1;
-                if (it + 1 < n_it) unit_at(it + 1, next_key, qt_unused);
-                if (next_key != key) umma_commit(bar(kPEmpty));   // last use of this query block
+                if (n + 1 == n_it || it.next_key() != key) umma_commit(bar(kPEmpty));   // last use of this query block
             }
         }
     } else {
@@ -275,12 +271,15 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
         const int kk = (K1 ? 2 : 0) + (K0 ? 1 : 0);
         const bool B0 = (c & 2) != 0, B1 = (r & 2) != 0;       // position of that 2x2 block inside its 4x4 block
         const bool do1 = P.level1 != nullptr && !(P.skip & 2), do2 = do1 && P.level2 != nullptr && !(P.skip & 4);
-        long t = 0;
-        for (long it = 0; it < n_it; ++it, ++t) {
-            long key;
-            int qt;
-            unit_at(it, key, qt);
-            const int pb = (int)(key % P.PB), b = (int)(key / P.PB);
+        int t = 0, cur_key = -1, pb = 0, b = 0;
+        UnitIter it = it0;
+        for (int n = 0; n < n_it; ++n, ++t, it.next()) {
+            const int key = it.key, qt = it.qt;
+            if (key != cur_key) {
+                cur_key = key;
+                b = key / P.PB;
+                pb = key - b * P.PB;
+            }
             const int ty = qt / P.qt_x, tx = qt - ty * P.qt_x;
             const int acc = (int)(t & 1);
             mbar_wait(bar(kAccFull + acc), (uint32_t)((t >> 1) & 1));
@@ -317,7 +316,11 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < EPQ; ++j) v[j] = __fdiv_rn(v[j], P.div);
             }
-            if (!(P.skip & 1)) {
+            if (P.skip & 1) {
+            } else if (n_valid == EPQ) {                      // the common case: no per-store predicate
+#pragma unroll
+                for (int j = 0; j < EPQ; ++j) o0[(unsigned)j * (unsigned)HW] = v[j];
+            } else {
 #pragma unroll
                 for (int j = 0; j < EPQ; ++j)
                     if (j < n_valid) o0[(unsigned)j * (unsigned)HW] = v[j];
@@ -557,6 +560,7 @@ int launch_corr_tc2(const void* f1, const void* f2, int in_dtype, int in_layout,
         tmPl = tmPh;
         if (split && (rc = make_tmap_bf16(&tmPl, l1, 3, dims, str, box))) return rc;
     }
+    if (P.units >= (1L << 31)) return fail(CF_ERR_UNSUPPORTED, "corr build: %ld tiles in one launch", P.units);
     const int grid = (int)min((long)sm_count(), P.units);
     // the opt-in to large dynamic shared memory belongs to the device: once per (device, kernel), sized for C = 256
     if (split) {

@@ -31,7 +31,7 @@ constexpr int QB_H = 8, QB_W = 16;         // query block: 8 rows x 16 columns o
 constexpr int CH_H = 8, CH_W = 16;         // position chunk: 8 rows x 16 columns of a pooled fmap2 level
 constexpr int NQ = 128, NPOS = 128;
 constexpr int BK = 64, UK = 16;
-constexpr int NSTAGE = 4;
+constexpr int NSTAGE = 5;
 constexpr int EPI_WARPS = 8, NTHREADS = 64 + 32 * EPI_WARPS;   // two epilogue threads per query
 constexpr int TMEM_COLS = 2 * NPOS;
 constexpr int MAX_KB = 4;

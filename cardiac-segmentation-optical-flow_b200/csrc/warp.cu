@@ -259,12 +259,14 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_kernel(const float* 
 // COUNT: also accumulate counts[b][c] = number of pixels of image b whose warped label is c (the per-frame class areas the
 // cohort scripts derive from the warped masks): one ballot per class per warp, one global atomic per (warp, class present).
 // Whole warps stay alive in that variant (columns beyond W are predicated off instead of returning).
-template <bool FASTDIV, bool COUNT>
+// OutT: int64 (the reference's argmax dtype) or uint8 (registered label maps as the cohort scripts store and gather them).
+template <bool FASTDIV, bool COUNT, typename OutT = int64_t>
 __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const float* __restrict__ flow,
                                                                          const int64_t* __restrict__ label,
-                                                                         int64_t* __restrict__ out, int ncls, int B, int H,
+                                                                         OutT* __restrict__ out, int ncls, int B, int H,
                                                                          int W, float ry, float rx,
-                                                                         unsigned long long* __restrict__ counts) {
+                                                                         unsigned long long* __restrict__ counts,
+                                                                         int counts_total = 0 /* 1: one [ncls] row for the whole batch */) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int x = blockIdx.x * kTileW + lane;
     const int y0 = blockIdx.y * kTileH + wid * 2;
@@ -283,7 +285,7 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
     for (unsigned b = blockIdx.z; b < (unsigned)B; b += gridDim.z) {
         const float* fl = flow + (size_t)b * 2 * HW;
         const int64_t* lb = label + (size_t)b * HW;
-        int64_t* ob = out + (size_t)b * HW;
+        OutT* ob = out + (size_t)b * HW;
         int won[2] = {-1, -1};
 #pragma unroll
         for (int rr = 0; rr < 2; ++rr) {
@@ -320,7 +322,8 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
                     best = c;
                 }
             }
-            __stcs(reinterpret_cast<long long*>(ob + pix), (long long)best);
+            if (sizeof(OutT) == 8) __stcs(reinterpret_cast<long long*>(ob + pix), (long long)best);
+            else ob[pix] = (OutT)best;
             won[rr] = best;
         }
         if (COUNT) {
@@ -328,7 +331,7 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
                 const int n = __popc(__ballot_sync(0xffffffffu, won[0] == c)) + __popc(__ballot_sync(0xffffffffu, won[1] == c));
                 if (lane == 0 && n) {
                     if (cta_agg) atomicAdd(&cta_cnt[c], (unsigned)n);
-                    else atomicAdd(counts + (size_t)b * ncls + c, (unsigned long long)n);
+                    else atomicAdd(counts + (size_t)(counts_total ? 0 : b) * ncls + c, (unsigned long long)n);
                 }
             }
             if (cta_agg) {      // 8 warps -> one global atomic per class present in this CTA's tile (was: one per warp)
@@ -336,7 +339,7 @@ __global__ void __launch_bounds__(256) warp2d_onehot_argmax_tile_kernel(const fl
                 if (threadIdx.x < ncls) {
                     const unsigned n = cta_cnt[threadIdx.x];
                     cta_cnt[threadIdx.x] = 0u;
-                    if (n) atomicAdd(counts + (size_t)b * ncls + threadIdx.x, (unsigned long long)n);
+                    if (n) atomicAdd(counts + (size_t)(counts_total ? 0 : b) * ncls + threadIdx.x, (unsigned long long)n);
                 }
                 __syncthreads();
             }
@@ -406,6 +409,29 @@ int launch_warp2d_taps(const float* flow, int B, int H, int W, float* taps, cuda
     const long total = (long)B * H * W;
     warp2d_taps_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, taps, H, W, 1.0f / (float)(H - 1), 1.0f / (float)(W - 1), total);
     CF_CHECK_LAUNCH("warp2d_taps_kernel");
+    return CF_OK;
+}
+
+int launch_warp2d_onehot_argmax_u8(const float* flow, const int64_t* label, int ncls, int B, int H, int W, uint8_t* out,
+                                   int64_t* counts, int counts_total, cudaStream_t s) {
+    const float ry = 1.0f / (float)(H - 1), rx = 1.0f / (float)(W - 1);
+    const int tx = cdiv(W, kTileW), ty = cdiv(H, kTileH);
+    if (!((long)H * W < (1L << 30) && ty <= 65535)) return fail(CF_ERR_UNSUPPORTED, "warp2d_onehot_argmax_u8: image of %dx%d pixels too large", H, W);
+    if (ncls > 256) return fail(CF_ERR_UNSUPPORTED, "warp2d_onehot_argmax_u8: %d classes do not fit uint8", ncls);
+    long gz = (4736 + (long)tx * ty - 1) / ((long)tx * ty);
+    gz = gz < 1 ? 1 : (gz > B ? B : (gz > 65535 ? 65535 : gz));
+    const dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)gz);
+    const bool fast = H - 1 <= 4095 && W - 1 <= 4095;
+    unsigned long long* cn = reinterpret_cast<unsigned long long*>(counts);
+    if (counts) {
+        CF_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * (size_t)(counts_total ? 1 : B) * ncls, s));
+        if (fast) warp2d_onehot_argmax_tile_kernel<true, true, uint8_t><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, cn, counts_total);
+        else warp2d_onehot_argmax_tile_kernel<false, true, uint8_t><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, cn, counts_total);
+    } else {
+        if (fast) warp2d_onehot_argmax_tile_kernel<true, false, uint8_t><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, nullptr);
+        else warp2d_onehot_argmax_tile_kernel<false, false, uint8_t><<<grid, 256, 0, s>>>(flow, label, out, ncls, B, H, W, ry, rx, nullptr);
+    }
+    CF_CHECK_LAUNCH("warp2d_onehot_argmax_tile_kernel<uint8>");
     return CF_OK;
 }
 

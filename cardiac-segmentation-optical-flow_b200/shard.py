@@ -5,8 +5,8 @@ temporal recurrence of the reference lives inside one (patient, slice) cine
 (/root/reference/nnunet/network_architecture/SegFlowGaussian.py:905-945; slices :3268; patients in the trainer
 :982).  So the unit of work is one (patient, slice) cine of T frames = T-1 pairs, units are dealt round-robin
 to ranks (one process per GPU), nothing is communicated while computing, and ONE gather at the end collects
-the compact per-unit results (registered label maps / metrics) over NCCL (NVLink 5 / NVSwitch) -- gloo on CPU
-in the tests.
+the per-unit results (registered label maps, uint8; metrics) over NCCL (NVLink 5 / NVSwitch) -- gloo on CPU
+in the tests.  The kernels write those results straight into this rank's slice of the all-gather buffer (GatherBuffer).
 """
 import torch
 import torch.distributed as dist
@@ -29,11 +29,49 @@ def shard_units(units, rank, world_size):
     return units[rank::world_size]
 
 
-def gather_results(local, n_units_total, rank=None, world_size=None, group=None):
-    """All-gather per-unit result rows.  ``local`` [n_local, ...] holds this rank's units in shard order; the
-    return value [n_units_total, ...] is in the global unit order on every rank.  Shards are padded to the
-    largest shard so one equal-size all_gather suffices (no staging copy: the padded buffer is the send buffer).
+class GatherBuffer:
+    """The receive buffer of the final all-gather, allocated up front so that the kernels write their per-unit results
+    STRAIGHT into this rank's slice (no staging copy precedes the collective; NCCL's in-place all-gather: the send buffer is
+    ``recv[rank]``).  Layout [world, per_rank, *item_shape]; rank r, slot j holds global unit j * world + r (round-robin
+    shards, padded to the largest shard).
+
+        buf = GatherBuffer(n_units_total, (29, 1, 256, 256), torch.uint8, device)
+        for j, unit in enumerate(my_units): kernel(..., out=buf.local[j])
+        table = buf.gather()            # [per_rank, world, *item_shape]: a transposed VIEW of the receive buffer (no copy)
+        item = buf.unit(table, k)       # result of global unit k
     """
+
+    def __init__(self, n_units_total, item_shape, dtype, device, rank=None, world_size=None, group=None):
+        if world_size is None:
+            world_size = dist.get_world_size(group) if dist.is_initialized() else 1
+        if rank is None:
+            rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.rank, self.world, self.group, self.n_total = rank, world_size, group, n_units_total
+        self.per_rank = (n_units_total + world_size - 1) // world_size
+        self.recv = torch.zeros((world_size, self.per_rank) + tuple(item_shape), dtype=dtype, device=device)
+        self.local = self.recv[rank]                       # this rank's slice = the send buffer
+
+    @property
+    def nbytes_sent(self):
+        return self.local.numel() * self.local.element_size()
+
+    def gather(self):
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.recv.view(-1), self.local.reshape(-1), group=self.group)
+        return self.recv.transpose(0, 1)                   # [slot j, rank r] = global unit j * world + r
+
+    def unit(self, table, k):
+        """Item of global unit k in what ``gather`` returned."""
+        if not 0 <= k < self.n_total:
+            raise IndexError(k)
+        return table[k // self.world, k % self.world]
+
+
+def gather_results(local, n_units_total, rank=None, world_size=None, group=None):
+    """All-gather per-unit result rows.  ``local`` [n_local, ...] holds this rank's units in shard order; the return value
+    [n_units_total, ...] is in the global unit order on every rank.  Convenience form for SMALL rows (it pads ``local`` into
+    an equal-size send buffer and reorders the result: two copies of the payload); results of any size should be produced
+    directly inside a ``GatherBuffer``."""
     if world_size is None:
         world_size = dist.get_world_size(group) if dist.is_initialized() else 1
     if rank is None:

@@ -75,11 +75,13 @@ def warp(src, flow, mode="bilinear", out=None):
     return _Warp2d.apply(flow, src, _MODES[mode], out)
 
 
-def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False, counts_out=None):
+def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False, counts_out=None, counts_total=False):
     """argmax_c warp(one_hot(label), flow) without the one-hot intermediate (the `warp_linear` pattern,
     SegFlowGaussian.py:3571-3580).  label [B,1,H,W] integer; returns int64 [B,1,H,W] (written into ``out`` when given).
     ``return_counts=True`` also returns int64 [B, num_classes]: pixels per class of every warped map, from the same launch
-    (written into ``counts_out`` when given: e.g. a row slice of a per-cine table that several lanes fill)."""
+    (written into ``counts_out`` when given: e.g. a row slice of a per-cine table that several lanes fill).
+    A uint8 ``out`` selects the 1-byte label maps (cf_warp2d_onehot_argmax_u8; ``counts_total=True``: one int64 [num_classes]
+    row for the whole batch instead of one per frame)."""
     if label.dim() != 4 or label.shape[1] != 1 or label.shape[0] != flow.shape[0] or label.shape[2:] != flow.shape[2:]:
         raise ValueError(f"label must be [B, 1, H, W] matching flow {tuple(flow.shape)}, got {tuple(label.shape)}")
     _cabi.require_cuda(flow, label)
@@ -88,8 +90,25 @@ def warp_onehot_argmax(flow, label, num_classes=4, out=None, return_counts=False
     B, _, H, W = lab.shape
     if out is None:
         out = torch.empty_like(lab)
-    elif out.dtype != torch.int64 or out.shape != lab.shape or not out.is_contiguous() or out.device != lab.device:
-        raise ValueError("out must be a contiguous int64 tensor of the label's shape on the same device")
+    elif (out.dtype not in (torch.int64, torch.uint8) or out.shape != lab.shape or not out.is_contiguous()
+          or out.device != lab.device):
+        raise ValueError("out must be a contiguous int64 (or uint8) tensor of the label's shape on the same device")
+    if out.dtype == torch.uint8:          # registered label maps, 1 byte per pixel (e.g. a slice of an all-gather buffer)
+        if lab.numel() == 0:
+            return (out, counts_out) if return_counts else out
+        counts = None
+        if return_counts:
+            cshape = (num_classes,) if counts_total else (B, num_classes)     # class areas of the whole batch / per frame
+            counts = counts_out if counts_out is not None else torch.empty(cshape, dtype=torch.int64, device=lab.device)
+            if (counts.dtype != torch.int64 or tuple(counts.shape) != cshape or not counts.is_contiguous()
+                    or counts.device != lab.device):
+                raise ValueError(f"counts_out must be a contiguous int64 {list(cshape)} tensor on the label's device")
+        with torch.cuda.device(f.device):
+            _cabi.check(_cabi.lib().cf_warp2d_onehot_argmax_u8(f.data_ptr(), lab.data_ptr(), num_classes, B, H, W, out.data_ptr(),
+                                                               counts.data_ptr() if counts is not None else None,
+                                                               1 if counts_total else 0, _cabi.stream()),
+                        "cf_warp2d_onehot_argmax_u8")
+        return (out, counts) if return_counts else out
     if lab.numel() == 0:                      # empty batch: nothing to warp (argmax of an empty one-hot stack is empty)
         if return_counts:
             return out, (counts_out if counts_out is not None else torch.zeros(B, num_classes, dtype=torch.int64, device=lab.device))

@@ -162,6 +162,14 @@ CF_API int cf_warp2d_onehot_argmax(const float* flow, const int64_t* label, int 
 CF_API int cf_warp2d_onehot_argmax_counts(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
                                    int64_t* out, int64_t* counts, void* stream);
 
+/* Same with a uint8 result (num_classes <= 256): the registered label maps as the cohort scripts keep them
+ * (compute_SSIM.py:26-104 loops per (patient, slice, frame)) and as the multi-GPU driver gathers them -- the kernel writes
+ * straight into the rank's slice of the NCCL all-gather buffer, 1 byte per pixel instead of 8.  counts (may be NULL) is
+ * int64 [B, num_classes] (counts_total = 0: per frame) or int64 [num_classes] (counts_total = 1: class areas of the whole
+ * batch, e.g. of one cine); overwritten. */
+CF_API int cf_warp2d_onehot_argmax_u8(const float* flow, const int64_t* label, int num_classes, int B, int H, int W,
+                               uint8_t* out, int64_t* counts, int counts_total, void* stream);
+
 /* ---- 8(f) next rows ---------------------------------------------------------------------------------------------
  * Backward passes (autograd): gradients of the warp w.r.t. src and flow, of the lookup w.r.t. the pyramid,
  * of the pooling chain and of the correlation w.r.t. both feature maps.  grad_* outputs that accumulate

@@ -45,6 +45,43 @@ def _worker(rank, world, port, n_patients, n_slices, width, q):
         dist.destroy_process_group()
 
 
+def _worker_buffer(rank, world, port, n_units, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from cardioflow_b200.shard import GatherBuffer, cohort_units, shard_units
+        units = cohort_units(n_units, 1)
+        mine = shard_units(units, rank, world)
+        buf = GatherBuffer(len(units), (3, 5), torch.uint8, "cpu")
+        assert buf.local.data_ptr() == buf.recv[rank].data_ptr()            # results land in the send slice itself: no staging copy
+        for j, (p, _) in enumerate(mine):
+            buf.local[j].fill_(p + 1)                                         # "the kernel writes its label map here"
+        table = buf.gather()
+        ok = all(bool((buf.unit(table, k) == units[k][0] + 1).all()) for k in range(len(units)))
+        ok = ok and table.data_ptr() == buf.recv.data_ptr()                  # the gathered table is a view of the receive buffer
+        q.put((rank, ok, len(mine)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_units", [(2, 7), (2, 8), (3, 10)])
+def test_gather_buffer_is_in_place_and_ordered(world, n_units):
+    """GatherBuffer: per-unit results (uint8 label maps on the GPU) are written straight into this rank's slice of the all-gather
+    buffer; the collective is in place; global unit order is recovered by indexing, not by copying."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_buffer, args=(r, world, port, n_units, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in results)
+    assert sum(n for _, _, n in results) == n_units
+
+
 @pytest.mark.parametrize("world,n_patients,n_slices", [(2, 3, 3), (2, 4, 2), (3, 5, 2)])
 def test_gather_restores_global_unit_order(world, n_patients, n_slices):
     ctx = mp.get_context("spawn")

@@ -6,10 +6,11 @@ dispatch, no CPU fallback.  Import name: ``cardioflow_b200`` (alias package at t
 name carries a hyphen and cannot be imported directly).
 """
 from .corr import CorrBlock, coords_grid, lookup_taps
+from .local_corr import CorrVolume
 from .ncc import NCC
 from .shard import Lanes, lane_bounds
 from .upsample import upsample_flow, upsample_seg
 from .warp import SpatialTransformer, SpatialTransformerContour, VecInt, utils_warp, warp, warp_onehot_argmax, warp_taps
 
 __all__ = ["CorrBlock", "coords_grid", "lookup_taps", "SpatialTransformer", "SpatialTransformerContour", "VecInt",
-           "warp", "warp_onehot_argmax", "warp_taps", "upsample_flow", "upsample_seg", "utils_warp", "Lanes", "lane_bounds", "NCC"]
+           "warp", "warp_onehot_argmax", "warp_taps", "upsample_flow", "upsample_seg", "utils_warp", "Lanes", "lane_bounds", "NCC", "CorrVolume"]

@@ -56,6 +56,8 @@ _SIGNATURES = {
     "cf_vecint": (_I, [_P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_sample_points": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "cf_sample_points_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "cf_local_corr": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _c.c_float, _I, _P, _P]),
+    "cf_local_corr_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _c.c_float, _I, _P, _P, _P]),
     "cf_warp2d_xy": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
     "cf_warp2d_xy_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_upsample_convex": (_I, [_P, _P, _I, _I, _I, _I, _I, _c.c_float, _P, _P]),

@@ -373,6 +373,23 @@ int cf_sample_points_bwd(const float* locs, const float* src, const float* grad_
                                     (cudaStream_t)stream);
 }
 
+int cf_local_corr(const float* cur, const float* prev, int B, int C, int H, int W, int radius, int stride, float scale, int x_major,
+                  float* out, void* stream) {
+    CF_REQUIRE(cur && prev && out, CF_ERR_BAD_ARG, "cf_local_corr: null pointer");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && stride >= 1, CF_ERR_BAD_ARG, "cf_local_corr: bad shape B=%d C=%d H=%d W=%d stride=%d", B, C, H, W, stride);
+    CF_REQUIRE(out != cur && out != prev, CF_ERR_BAD_ARG, "cf_local_corr: out must not alias the inputs");
+    return launch_local_corr(cur, prev, B, C, H, W, radius, stride, scale, x_major != 0, out, (cudaStream_t)stream);
+}
+
+int cf_local_corr_bwd(const float* cur, const float* prev, const float* grad_out, int B, int C, int H, int W, int radius, int stride,
+                      float scale, int x_major, float* grad_cur, float* grad_prev, void* stream) {
+    CF_REQUIRE(cur && prev && grad_out, CF_ERR_BAD_ARG, "cf_local_corr_bwd: null pointer");
+    CF_REQUIRE(grad_cur || grad_prev, CF_ERR_BAD_ARG, "cf_local_corr_bwd: neither gradient requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && stride >= 1, CF_ERR_BAD_ARG, "cf_local_corr_bwd: bad shape");
+    return launch_local_corr_bwd(cur, prev, grad_out, B, C, H, W, radius, stride, scale, x_major != 0, grad_cur, grad_prev,
+                                 (cudaStream_t)stream);
+}
+
 int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H, int W, float* out, void* stream) {
     CF_REQUIRE(flow && src && out, CF_ERR_BAD_ARG, "cf_warp2d_xy: null pointer");
     CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_warp2d_xy: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);

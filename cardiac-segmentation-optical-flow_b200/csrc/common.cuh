@@ -158,4 +158,9 @@ int launch_lookup_tc_prepare(const float* f1, const float* f2, int B, int C, int
                              size_t ws_bytes, cudaStream_t s);
 int launch_lookup_tc(const void* operands, const float* coords, int B, int C, int H, int W, int L, int r, float* out,
                      cudaStream_t s);
+// local correlation layer (local_corr.cu; parity unpinned)
+int launch_local_corr(const float* cur, const float* prev, int B, int C, int H, int W, int r, int stride, float scale,
+                      int x_major, float* out, cudaStream_t s);
+int launch_local_corr_bwd(const float* cur, const float* prev, const float* go, int B, int C, int H, int W, int r, int stride,
+                          float scale, int x_major, float* gcur, float* gprev, cudaStream_t s);
 }  // namespace cf

@@ -549,6 +549,7 @@ int launch_lookup(const float* pyramid, const LevelDims& d, const float* coords,
     P.tiled = tiled_mask;
     static const float frac = [] { const char* e = getenv("CF_L2_FRAC"); return e ? (float)atof(e) : 1.0f; }();   // tuning knob
     P.l2_frac = frac;
+
     switch (r) {
         case 1: return launch_lookup_r<1>(P, s);
         case 2: return launch_lookup_r<2>(P, s);

@@ -216,6 +216,17 @@ CF_API int cf_warp2d_xy(const float* flow, const float* src, int B, int C, int H
 CF_API int cf_warp2d_xy_bwd(const float* flow, const float* src, const float* grad_out, int B, int C, int H, int W,
                      float* grad_src, float* grad_flow, void* stream);
 
+/* Local correlation layer (8(f) row 4, first half): `CorrVolume(radius, stride)(cur, prev)` of the reference's skip connections
+ * (SegFlowGaussian.py:41 import, :259 construction, :1376 call).  PARITY UNPINNED: its source nnunet/lib/raft.py was never
+ * committed; only the call-site contract [B,C,H,W] x [B,C,H,W] -> [B,(2r+1)^2,H,W] is known.  Implements the standard local cost
+ * volume out[b, (dy+r)*(2r+1) + (dx+r), y, x] = scale * sum_c cur[b,c,y,x] * prev[b,c,y+dy*stride,x+dx*stride], zero padding
+ * (x_major != 0: channel (dx+r)*(2r+1) + (dy+r), RAFT's lookup order).  1 <= radius <= CF_MAX_RADIUS.
+ * Backward: grad_cur / grad_prev [B,C,H,W] are written (either may be NULL). */
+CF_API int cf_local_corr(const float* cur, const float* prev, int B, int C, int H, int W, int radius, int stride, float scale,
+                  int x_major, float* out, void* stream);
+CF_API int cf_local_corr_bwd(const float* cur, const float* prev, const float* grad_out, int B, int C, int H, int W, int radius,
+                      int stride, float scale, int x_major, float* grad_cur, float* grad_prev, void* stream);
+
 /* Convex 8x upsampling (8(f) row 3): replaces `upsample_flow` (SegFlowGaussian.py:846-857, C = 2) and `upsample_seg`
  * (:860-871, C = 4): out[n,c,8y+i,8x+j] = sum_k softmax_k(mask[n,k*64+i*8+j,y,x]) * scale * field[n,c,y+ky-1,x+kx-1],
  * k = ky*3+kx, zeros outside.  field [B,C,H,W], mask [B,576,H,W], out [B,C,8H,8W]; the reference passes scale = 8

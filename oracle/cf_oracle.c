@@ -46,7 +46,13 @@ static inline float bilinear(const float* img, int h, int w, float uy, float ux)
     float wxh = ux - fx, wxl = (fx + 1.0f) - ux;
     float wyh = uy - fy, wyl = (fy + 1.0f) - uy;
     /* ATen's CUDA grid_sampler accumulates `out += val * weight`, which nvcc contracts to FMA; the reference
-     * ran on a GPU, so the restatement uses fmaf explicitly (the weight products are plain multiplies). */
+     * ran on a GPU, so the restatement uses fmaf explicitly (the weight products are plain multiplies).
+     * Measured against ATen-CUDA itself on a B200 (tools/aten_cuda_probe.py, tests/test_gpu_aten_cuda.py, round 2): this
+     * sequence is bit-identical on 89.1 % of the outputs and within 1.8e-7 (one ulp of the output scale) on the rest.  nvcc
+     * happens to keep the NE product as the rounded multiply and to fuse NW into it (the sum of the first two products is
+     * commutative, so either contraction is legal): fma(se, fma(sw, fma(nw, ne*w_ne))) matches 98.6 %; no fixed sequence
+     * matches 100 % (the bounds-check branches change which product is fused).  The nw-first order is kept: it is the
+     * source order of both ATen kernels and the difference is below every stated tolerance. */
     float acc = fetch(img, h, w, y0, x0) * (wxl * wyl);
     acc = fmaf(fetch(img, h, w, y0, x0 + 1), wxh * wyl, acc);
     acc = fmaf(fetch(img, h, w, y0 + 1, x0), wxl * wyh, acc);

@@ -2,10 +2,11 @@
 
 The reference's ``nnunet``, ``nnunet.lib`` and ``nnunet.network_architecture`` are regular packages (they have
 ``__init__.py``), so a same-named directory earlier on ``PYTHONPATH`` is never consulted for their sub-modules.  This
-finder sits at the front of ``sys.meta_path`` instead and answers for exactly two module names:
+finder sits at the front of ``sys.meta_path`` instead and answers for exactly three module names:
 
     nnunet.lib.raft_initial                    (imported at nnunet/network_architecture/SegFlowGaussian.py:42)
     nnunet.network_architecture.integration    (imported by 10+ files, e.g. SegFlowGaussian.py:35)
+    nnunet.lib.raft                            (CorrVolume, SegFlowGaussian.py:41; the file is missing upstream)
 
 with the files under ``shim/nnunet/...``, which re-export the cardioflow_b200 classes and pass every OTHER name
 (``BasicUpdateBlock``, ...) through from the module the reference tree itself provides under that name.
@@ -24,6 +25,7 @@ REPO_ROOT = os.path.dirname(SHIM_DIR)
 TARGETS = {
     "nnunet.lib.raft_initial": os.path.join(SHIM_DIR, "nnunet", "lib", "raft_initial.py"),
     "nnunet.network_architecture.integration": os.path.join(SHIM_DIR, "nnunet", "network_architecture", "integration.py"),
+    "nnunet.lib.raft": os.path.join(SHIM_DIR, "nnunet", "lib", "raft.py"),     # CorrVolume (SegFlowGaussian.py:41; parity unpinned)
 }
 
 

@@ -192,6 +192,35 @@ def test_full_size_properties_cfg4():
     assert np.abs(blk(coords)[:1].cpu().numpy() - want).max() <= 2e-5 * np.abs(want).max()
 
 
+def test_full_batch_cfg4_whole_batch():
+    """BASELINE cfg 4 at full size, the WHOLE batch (64 pairs, 256 channels, 64x64 fmaps; 5.7 GB pyramid): (1) level 0 of the
+    fp32-grade tensor-core build (bf16x3) within 1e-5 of a CPU fp32 matmul for every pair; (2) pooled levels bit-identical to
+    avg_pool2d; (3) lookups of all 64 x 4096 queries BIT-EXACT against the C oracle run on the pyramid the GPU built (tiled
+    levels 0 and 1 un-tiled through corr_pyramid)."""
+    b, c, h, w = 64, 256, 64, 64
+    g = torch.Generator().manual_seed(1004)
+    f1, f2 = torch.randn(b, c, h, w, generator=g), torch.randn(b, c, h, w, generator=g)
+    grid = corr_oracle.coords_grid(b, h, w)
+    coords = grid + torch.randn(b, 2, h, w, generator=g) * 2.0
+    with torch.no_grad():
+        blk = cf.CorrBlock(f1.to(DEV), f2.to(DEV))
+        assert blk.used_precision == "bf16x3" and blk._tiled_mask == 3
+        out = blk(coords.to(DEV)).cpu().numpy()
+        pyr = [p.cpu() for p in blk.corr_pyramid]
+    del blk
+    torch.cuda.empty_cache()
+    worst = 0.0
+    for i in range(b):                                   # CPU fp32 reference, pair by pair (bounded memory)
+        want = torch.matmul(f1[i].view(c, -1).t(), f2[i].view(c, -1)) / 16.0
+        got = pyr[0][i * h * w:(i + 1) * h * w, 0].reshape(h * w, h * w)
+        worst = max(worst, float((got - want).abs().max()) / float(want.abs().max()))
+    assert worst <= 1e-5, worst
+    for l in range(1, 4):
+        assert torch.equal(pyr[l], torch.nn.functional.avg_pool2d(pyr[l - 1], 2, stride=2)), l
+    want_c = c_oracle.lookup([p.numpy() for p in pyr], coords.numpy())
+    assert np.array_equal(out, want_c)
+
+
 @pytest.mark.parametrize("hw,c,want_mask", [((64, 64), 128, 3), ((32, 64), 64, 3), ((64, 32), 256, 1), ((40, 96), 32, 3), ((64, 128), 32, 3),
                                             ((36, 72), 40, 1), ((16, 16), 64, 0)])
 def test_tiled_levels_generic_epilogue(monkeypatch, hw, c, want_mask):

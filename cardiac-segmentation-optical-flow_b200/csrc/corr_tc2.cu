@@ -94,21 +94,25 @@ namespace {
 using namespace tc;
 
 constexpr int TQ = 128;          // fmap2 positions per tile (UMMA M): 4 rows x 32 columns
-constexpr int NP = 128;          // queries per block (UMMA N)
+constexpr int NPS = 128;         // queries per sub-block; a resident block is NB sub-blocks = UMMA N of 128 or 256
 constexpr int BK = 64, UK = 16;  // channels per ring stage / per MMA
 constexpr int EPI_WARPS = 16;         // four per TMEM lane quadrant
-constexpr int EPQ = NP * 4 / EPI_WARPS;   // queries per epilogue warp (32: one tcgen05.ld x32)
+constexpr int EPQ = 32;               // queries per epilogue warp and sub-block (one tcgen05.ld x32)
 constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
-constexpr int TMEM_COLS = 2 * NP;   // two accumulators
 constexpr int MAX_KB = 4;           // C <= 256
 constexpr uint32_t OP_BYTES = 128u * 128u;   // one 128-row x 64-channel bf16 operand block
 
-template <bool SPLIT> struct Cfg {
+// NB = 2 (plain bf16 only: the split operands would not fit): 256 queries resident, every q stage feeds ONE N = 256 MMA, so the
+// operand re-reads from L2 are halved.  Measured slower than NB = 1 (see launch_corr_tc2): an experiment knob, not the default.
+template <bool SPLIT, int NB> struct Cfg {
+    static_assert(NB == 1 || (NB == 2 && !SPLIT), "two sub-blocks only without the lo parts");
     static constexpr int PARTS = SPLIT ? 2 : 1;          // hi (+ lo)
-    static constexpr int NSTAGE = SPLIT ? 3 : 6;           // (9 stages measured no faster than 5: the kernel is L2-throughput bound)
+    static constexpr int NSTAGE = SPLIT ? 3 : (NB == 2 ? 5 : 6);   // (9 stages measured no faster than 5: L2-throughput bound)
+    static constexpr int NP = NPS * NB;                  // UMMA N
+    static constexpr int TMEM_COLS = 2 * NP;             // two accumulators
     static constexpr uint32_t STAGE_BYTES = OP_BYTES * PARTS;
     static constexpr size_t smem_bytes(int k_blocks) {
-        return 1024 + (size_t)k_blocks * OP_BYTES * PARTS + (size_t)NSTAGE * STAGE_BYTES + 256;
+        return 1024 + (size_t)k_blocks * OP_BYTES * PARTS * NB + (size_t)NSTAGE * STAGE_BYTES + 256;
     }
 };
 
@@ -130,22 +134,22 @@ __device__ __forceinline__ float pool4(float a, float b, float c, float d) {
     return __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(a, b), c), d), 0.25f);   // avg_pool2d order; /4 is exact as *0.25
 }
 
-template <bool SPLIT>
+template <bool SPLIT, int NB>
 __global__ void __launch_bounds__(NTHREADS, 1)
 corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant__ CUtensorMap tmQl,
                 const __grid_constant__ CUtensorMap tmPh, const __grid_constant__ CUtensorMap tmPl, const G2Params P) {
-    using K = Cfg<SPLIT>;
-    constexpr int NSTAGE = K::NSTAGE;
+    using K = Cfg<SPLIT, NB>;
+    constexpr int NSTAGE = K::NSTAGE, NP = K::NP, TMEM_COLS = K::TMEM_COLS;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint32_t tmem_base_slot;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t s_res = base;                                                        // [part][kb][128 x 128 B]
-    const uint32_t s_ring = s_res + (uint32_t)P.k_blocks * OP_BYTES * K::PARTS;          // [stage][part][128 x 128 B]
+    const uint32_t s_ring = s_res + (uint32_t)P.k_blocks * OP_BYTES * K::PARTS * NB;     // [stage][part][128 x 128 B]
     const uint32_t s_bars = s_ring + (uint32_t)NSTAGE * K::STAGE_BYTES;
     constexpr int kFull = 0, kEmpty = NSTAGE, kPFull = 2 * NSTAGE, kPEmpty = 2 * NSTAGE + 1, kAccFull = 2 * NSTAGE + 2,
                   kAccEmpty = 2 * NSTAGE + 4;
     auto bar = [&](int i) { return s_bars + 8u * (uint32_t)i; };
-    auto res = [&](int part, int kb) { return s_res + (uint32_t)(part * P.k_blocks + kb) * OP_BYTES; };
+    auto res = [&](int part, int kb) { return s_res + (uint32_t)((part * P.k_blocks + kb) * NB) * OP_BYTES; };   // NB x 128 rows, contiguous
     auto ring = [&](int stage, int part) { return s_ring + (uint32_t)stage * K::STAGE_BYTES + (uint32_t)part * OP_BYTES; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -194,11 +198,13 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
                     pb = key - b * P.PB;
                     // the MMAs of the previous query block must have retired before its operand is overwritten
                     if (n_res > 0) mbar_wait(bar(kPEmpty), (uint32_t)((n_res - 1) & 1));
-                    mbar_expect_tx(bar(kPFull), (uint32_t)P.k_blocks * OP_BYTES * K::PARTS);
-                    for (int kb = 0; kb < P.k_blocks; ++kb) {
-                        tma_load_3d(res(0, kb), &tmPh, bar(kPFull), kb * BK, pb * NP, b);
-                        if (SPLIT) tma_load_3d(res(1, kb), &tmPl, bar(kPFull), kb * BK, pb * NP, b);
-                    }
+                    mbar_expect_tx(bar(kPFull), (uint32_t)P.k_blocks * OP_BYTES * K::PARTS * NB);
+                    for (int kb = 0; kb < P.k_blocks; ++kb)
+#pragma unroll
+                        for (int nb = 0; nb < NB; ++nb) {
+                            tma_load_3d(res(0, kb) + (uint32_t)nb * OP_BYTES, &tmPh, bar(kPFull), kb * BK, pb * NP + nb * NPS, b);
+                            if (SPLIT) tma_load_3d(res(1, kb) + (uint32_t)nb * OP_BYTES, &tmPl, bar(kPFull), kb * BK, pb * NP + nb * NPS, b);
+                        }
                     cur_key = key;
                     ++n_res;
                 }
@@ -284,25 +290,28 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
             const int acc = (int)(t & 1);
             mbar_wait(bar(kAccFull + acc), (uint32_t)((t >> 1) & 1));
             tc_fence_after();
-            float v[EPQ];
-            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NP + part * EPQ), v);
-            tmem_wait_ld();
-            // the accumulator is in registers: hand the TMEM buffer back to the MMA warp right away
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(kAccEmpty + acc));
-
             const int x0 = 32 * tx + 8 * quad;
             const int y = 4 * ty + r, x = x0 + c;
-            const int p_first = pb * NP + part * EPQ;           // first query of this warp's share
-            const int n_valid = min(EPQ, HW - p_first);         // warp-uniform; <= 0 when the block hangs over the map
-            if (x0 >= W || n_valid <= 0) continue;              // warp-uniform (W is a multiple of 8)
             const size_t q0 = P.tile_l0 ? (size_t)(((y >> 2) * (W >> 2) + (x >> 2)) * 16 + (y & 3) * 4 + (x & 3))
                                         : (size_t)y * W + x;
             const int y1 = y >> 1, x1 = x >> 1;
             const size_t q1 = P.tile_l1 ? (size_t)(((y1 >> 2) * (w1 >> 2) + (x1 >> 2)) * 16 + (y1 & 3) * 4 + (x1 & 3))
                                         : (size_t)y1 * w1 + x1;
             const size_t q2 = (size_t)(y >> 2) * w2 + (x >> 2);
+#pragma unroll 1
+          for (int nb = 0; nb < NB; ++nb) {
+            float v[EPQ];
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * NP + nb * NPS + part * EPQ), v);
+            tmem_wait_ld();
+            if (nb == NB - 1) {
+                // the last of this warp's accumulator columns are in registers: hand the TMEM buffer back to the MMA warp
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(kAccEmpty + acc));
+            }
+            const int p_first = pb * NP + nb * NPS + part * EPQ;   // first query of this warp's share of the sub-block
+            const int n_valid = min(EPQ, HW - p_first);         // warp-uniform; <= 0 when the block hangs over the map
+            if (x0 >= W || n_valid <= 0) continue;              // warp-uniform (W is a multiple of 8)
             const size_t img = (size_t)b * HW + p_first;        // first image (query) index of this warp
             float* const o0 = P.level0 + img * HW + q0;
             float* const o1 = do1 ? P.level1 + img * img1 + q1 : nullptr;
@@ -356,6 +365,7 @@ corr_tc2_kernel(const __grid_constant__ CUtensorMap tmQh, const __grid_constant_
                     }
                 }
             }
+          }   // sub-blocks
         }
     }
 
@@ -525,6 +535,12 @@ int launch_corr_tc2(const void* f1, const void* f2, int in_dtype, int in_layout,
     P.k_blocks = (C + BK - 1) / BK;
     P.qt_x = (W + 31) / 32;
     P.QT = P.qt_x * (H / 4);
+    // Two 128-query sub-blocks per resident block (N = 256, plain bf16 only) halve the operand re-reads -- and measured SLOWER:
+    // 78.4 vs 74.5 us at cfg2, 1784 vs 1552 us at cfg4 (the accumulator is held until the second half is read and the epilogue,
+    // not the operand stream, is what the tile time follows).  Kept behind CF_TC2_NB=2 as the evidence; the default is one.
+    static const int nb_knob = [] { const char* e = getenv("CF_TC2_NB"); return e ? atoi(e) : 1; }();   // tuning knob
+    const int NB = (nb_knob == 2 && !split) ? 2 : 1;
+    const int NP = NPS * NB;
     P.PB = (HW + NP - 1) / NP;
     P.units = (long)B * P.PB * P.QT;
     P.div = sqrtf((float)C);
@@ -555,7 +571,7 @@ int launch_corr_tc2(const void* f1, const void* f2, int in_dtype, int in_layout,
     {   // fmap1 as (channels, position, batch)
         const uint64_t dims[3] = {(uint64_t)C, (uint64_t)HW, (uint64_t)B};
         const uint64_t str[2] = {rb, rb * HW};
-        const uint32_t box[3] = {BK, NP, 1};
+        const uint32_t box[3] = {BK, NPS, 1};
         if ((rc = make_tmap_bf16(&tmPh, h1, 3, dims, str, box))) return rc;
         tmPl = tmPh;
         if (split && (rc = make_tmap_bf16(&tmPl, l1, 3, dims, str, box))) return rc;
@@ -564,11 +580,14 @@ int launch_corr_tc2(const void* f1, const void* f2, int in_dtype, int in_layout,
     const int grid = (int)min((long)sm_count(), P.units);
     // the opt-in to large dynamic shared memory belongs to the device: once per (device, kernel), sized for C = 256
     if (split) {
-        if ((rc = smem_optin(reinterpret_cast<const void*>(&corr_tc2_kernel<true>), Cfg<true>::smem_bytes(MAX_KB), 0))) return rc;
-        corr_tc2_kernel<true><<<grid, NTHREADS, Cfg<true>::smem_bytes(P.k_blocks), s>>>(tmQh, tmQl, tmPh, tmPl, P);
+        if ((rc = smem_optin(reinterpret_cast<const void*>(&corr_tc2_kernel<true, 1>), Cfg<true, 1>::smem_bytes(MAX_KB), 0))) return rc;
+        corr_tc2_kernel<true, 1><<<grid, NTHREADS, Cfg<true, 1>::smem_bytes(P.k_blocks), s>>>(tmQh, tmQl, tmPh, tmPl, P);
+    } else if (NB == 2) {
+        if ((rc = smem_optin(reinterpret_cast<const void*>(&corr_tc2_kernel<false, 2>), Cfg<false, 2>::smem_bytes(MAX_KB), 2))) return rc;
+        corr_tc2_kernel<false, 2><<<grid, NTHREADS, Cfg<false, 2>::smem_bytes(P.k_blocks), s>>>(tmQh, tmQl, tmPh, tmPl, P);
     } else {
-        if ((rc = smem_optin(reinterpret_cast<const void*>(&corr_tc2_kernel<false>), Cfg<false>::smem_bytes(MAX_KB), 1))) return rc;
-        corr_tc2_kernel<false><<<grid, NTHREADS, Cfg<false>::smem_bytes(P.k_blocks), s>>>(tmQh, tmQl, tmPh, tmPl, P);
+        if ((rc = smem_optin(reinterpret_cast<const void*>(&corr_tc2_kernel<false, 1>), Cfg<false, 1>::smem_bytes(MAX_KB), 1))) return rc;
+        corr_tc2_kernel<false, 1><<<grid, NTHREADS, Cfg<false, 1>::smem_bytes(P.k_blocks), s>>>(tmQh, tmQl, tmPh, tmPl, P);
     }
     CF_CHECK_LAUNCH("corr_tc2_kernel");
     return CF_OK;

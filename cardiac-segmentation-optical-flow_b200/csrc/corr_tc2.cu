@@ -66,13 +66,13 @@ int make_tmap_bf16(CUtensorMap* m, const void* ptr, int rank, const uint64_t* di
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute of a kernel: set once per (device, slot)
 int smem_optin(const void* func, size_t bytes, int slot) {
     static std::mutex mu;
-    static bool done[64][16] = {};
+    static bool done[64][32] = {};
     int dev = 0;
     CF_CHECK_CUDA(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lock(mu);
-    if (dev >= 0 && dev < 64 && slot >= 0 && slot < 16 && done[dev][slot]) return CF_OK;
+    if (dev >= 0 && dev < 64 && slot >= 0 && slot < 32 && done[dev][slot]) return CF_OK;
     CF_CHECK_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    if (dev >= 0 && dev < 64 && slot >= 0 && slot < 16) done[dev][slot] = true;
+    if (dev >= 0 && dev < 64 && slot >= 0 && slot < 32) done[dev][slot] = true;
     return CF_OK;
 }
 

@@ -8,14 +8,16 @@
 // separate elementwise division over the whole volume and a pooling launch that re-reads it.
 //
 // Mapping to the hardware
-//   * A = f1[b]^T and B = f2[b] are stored [C, HW] with HW contiguous, i.e. "MN-major" operands.  tcgen05 accepts them
-//     for kind::f16 (kind::tf32 returns zeros, tools/umma_probe.cu), but measured on B200 an MN-major 128x128x16 MMA
-//     takes ~195 cycles instead of ~64-96 (per-role timeline, tools/gemm_ts.py): the kernel was MMA-issue bound.  So
-//     the bf16 rounding pre-pass also TRANSPOSES both maps to [B, HW, C] (one tiled pass, same bytes as before) and the
-//     MMA reads canonical K-major SWIZZLE_128B operands: TMA boxes of 64 channels (128 B) x rows, 8-row groups 1024 B
-//     apart (SBO), K advanced by 32 B inside the swizzle atom.  fp32 accumulate in TMEM.
+//   (Version 1 of the build, round 1.  Since round 2 cabi.cu uses it for plain bf16 at W = 32 and for shapes version 2,
+//   corr_tc2.cu, rejects; everything else -- the fp32-grade bf16x3 default, other widths, bf16 / channels-last inputs -- is v2.)
+//   * The caller's maps are [C, HW] with HW contiguous, i.e. "MN-major" operands.  tcgen05 accepts them for kind::f16
+//     (kind::tf32 returns zeros, tools/umma_probe.cu), but measured on B200 an MN-major 128x128x16 MMA takes ~195 cycles
+//     instead of ~64-96 (per-role timeline, tools/gemm_ts.py with -DCF_BRINGUP).  So the bf16 rounding pre-pass TRANSPOSES
+//     both maps to [B, HW, C] (one tiled pass) and the MMA reads canonical K-major SWIZZLE_128B operands: TMA boxes of 64
+//     channels (128 B) x rows, 8-row groups 1024 B apart (SBO), K advanced by 32 B inside the swizzle atom.  fp32 accumulate
+//     in TMEM.
 //   * one CTA owns a 128-row block of queries p for one frame pair: the A block (128 x C bf16 = 64 KB at
-//     C = 256) is loaded ONCE and stays resident; B streams through a 4-stage ring of 128(n) x 64(k) tiles;
+//     C = 256) is loaded ONCE and stays resident; B streams through a 5-stage ring (NSTAGE) of 128(n) x 64(k) tiles;
 //     accumulators (128 x BN fp32) are double-buffered in TMEM so the epilogue of tile t overlaps the MMAs of
 //     tile t+1.  Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-5 =
 //     epilogue (tcgen05.ld -> scale -> swizzled smem -> TMA store of level 0; second TMEM pass pools 2x2 over
@@ -29,7 +31,7 @@
 #include <cstdlib>
 #include <mutex>
 
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace cf {
 namespace {
@@ -618,7 +620,7 @@ int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, i
     // one CTA per SM at a time (smem): split the n range only until every SM has a CTA -- each CTA re-loads its 64 KB A
     // block before its first MMA, so fewer, longer CTAs win once the machine is full (measured at cfg2: 1 > 2 > 4)
     int split = 1;
-    while ((long)B * P.m_tiles * split < 148 && P.n_tiles / (split * 2) >= 1) split *= 2;
+    while ((long)B * P.m_tiles * split < sm_count() && P.n_tiles / (split * 2) >= 1) split *= 2;
     static const int force_split = [] { const char* e = getenv("CF_GEMM_SPLIT"); return e ? atoi(e) : 0; }();   // tuning knob
     if (force_split > 0 && P.n_tiles / force_split >= 1) split = force_split;
     P.n_split = split;
@@ -660,16 +662,13 @@ int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, i
                               (uint64_t)HW * (H / 2) * 64, 32, BM)))
         return rc;
     const size_t smem = 1024 + (size_t)((C + BK - 1) / BK) * BM * 128 + (size_t)NSTAGE * MAX_BN * 128 + NEPI * 128 * 128 + kNumBars * 8 + 64;
-    // opt in to the large dynamic shared memory once (sized for MAX_C; static smem counts against the 227 KB cap)
-    static std::once_flag attr_once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(attr_once, [] {
-        const int max_smem = 1024 + MAX_C * 256 + NSTAGE * MAX_BN * 128 + NEPI * 128 * 128 + kNumBars * 8 + 64;
-        attr_err = cudaFuncSetAttribute(corr_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (attr_err == cudaSuccess)
-            attr_err = cudaFuncSetAttribute(corr_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-    });
-    if (attr_err != cudaSuccess) return fail(CF_ERR_CUDA, "cudaFuncSetAttribute(max smem): %s", cudaGetErrorString(attr_err));
+    // opt in to the large dynamic shared memory (sized for MAX_C; a per-device attribute: once per device and kernel)
+    {
+        const size_t max_smem = 1024 + MAX_C * 256 + NSTAGE * MAX_BN * 128 + NEPI * 128 * 128 + kNumBars * 8 + 64;
+        int rc2 = smem_optin(reinterpret_cast<const void*>(&corr_tcgen05_kernel<false>), max_smem, 16);
+        if (!rc2) rc2 = smem_optin(reinterpret_cast<const void*>(&corr_tcgen05_kernel<true>), max_smem, 17);
+        if (rc2) return rc2;
+    }
     const long grid = (long)B * P.m_tiles * P.n_split;
     if (w32) corr_tcgen05_kernel<true><<<(unsigned)grid, NTHREADS, smem, s>>>(tmA, tmB, tmC, tmL1, P);
     else corr_tcgen05_kernel<false><<<(unsigned)grid, NTHREADS, smem, s>>>(tmA, tmB, tmC, tmL1, P);

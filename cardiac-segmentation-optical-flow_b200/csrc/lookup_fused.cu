@@ -15,8 +15,8 @@
 //       3. windows (scaled by 1/sqrt(C), zero outside the image) are interpolated from shared memory with
 //          the same exact tap arithmetic as the materialised lookup (sampling.cuh: axis_tap)
 // Results differ from the materialised fp32 path only by fp32 summation order (pool-then-dot vs dot-then-pool).
-#include "common.cuh"
 #include "sampling.cuh"
+#include "tc_common.cuh"
 
 namespace cf {
 
@@ -186,10 +186,9 @@ int launch_fused_r(const FusedParams& P, cudaStream_t s) {
     if (grid > 0x7fffffffL) return fail(CF_ERR_UNSUPPORTED, "fused lookup grid too large (%ld)", grid);
     const size_t smem = ((size_t)P.C * kQF + (size_t)kQF * (PR * PR + 1)) * sizeof(float);
     if (smem > 200 * 1024) return fail(CF_ERR_UNSUPPORTED, "fused lookup: C = %d needs %zu B of shared memory", P.C, smem);
-    static bool attr_set = false;   // idempotent; a race only repeats the call
-    if (!attr_set) {
-        CF_CHECK_CUDA(cudaFuncSetAttribute(lookup_fused_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
+    {   // a per-device attribute: once per device and kernel (tc_common.cuh)
+        const int rc = smem_optin(reinterpret_cast<const void*>(&lookup_fused_kernel<R>), 200 * 1024, 20 + R);
+        if (rc) return rc;
     }
     lookup_fused_kernel<R><<<(unsigned)grid, 32 * kNWF, smem, s>>>(P);
     CF_CHECK_LAUNCH("lookup_fused_kernel");

@@ -127,11 +127,12 @@ __device__ __noinline__ void warp2d_general(const float* __restrict__ img, float
 constexpr int kTileW = 32, kTileH = 16;   // CTA tile: 8 warps, each 32 pixels x 2 rows (lane = column)
 
 // UNROLL / MINB measured at cfg3 (300 x {1,5} x 224^2): (2,4) 77 / 210 us, (4,4) 102 / 255, (5,3) 96 / 241, (2,5) 73 / 206,
-// (1,6) 71 / 196: the kernel wants resident warps (40 registers, 6 CTAs per SM), not deeper unrolling.
+// (1,6) 71 / 196, (1,8) 69 / 175 (round 2, with 9800 CTAs): the kernel wants resident warps (32 registers, 8 CTAs per SM = the
+// 64-warp limit), not deeper unrolling.
 template <bool FASTDIV, int UNROLL = 1, int MINB = 6>
 __global__ void __launch_bounds__(256, MINB) warp2d_tile_kernel(const float* __restrict__ flow, const float* __restrict__ src,
                                                              float* __restrict__ out, int B, int C, int H, int W, float ry,
-                                                             float rx) {
+                                                             float rx, int pf_rows) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int x = blockIdx.x * kTileW + lane;
     const int y = blockIdx.y * kTileH + wid * 2;
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(256, MINB) warp2d_tile_kernel(const float* __r
     const unsigned HW = (unsigned)(H * W), pix = (unsigned)y * (unsigned)W + (unsigned)x;
     const float s1y = (float)(H - 1), s1x = (float)(W - 1), hs1y = 0.5f * s1y, hs1x = 0.5f * s1x;
     const float yf0 = (float)y, yf1 = (float)(y + 1), xf = (float)x;
+    const int wid_u = __shfl_sync(0xffffffffu, wid, 0);      // the warp index as a value the compiler knows to be warp-uniform
 
     // The chain flow load -> coordinates -> gathers -> store is two DRAM latencies long and a thread keeps only 16 B of
     // flow in flight: the flow of the NEXT image of this thread is loaded before the current one is sampled.
@@ -154,6 +156,22 @@ __global__ void __launch_bounds__(256, MINB) warp2d_tile_kernel(const float* __r
             const float* fyp = flow + ((size_t)(b + gridDim.z) * 2) * HW + pix;
             if (act0) { nfy0 = __ldcs(fyp); nfx0 = __ldcs(fyp + HW); }
             if (act1) { nfy1 = __ldcs(fyp + W); nfx1 = __ldcs(fyp + HW + W); }
+        }
+        // L2 prefetch of the source rows around this tile for the NEXT image of this CTA (a hint: 128 bytes per row and channel,
+        // the tile's own columns -- the margins are the neighbouring CTAs' columns): the gathers below then wait for L2, not DRAM.
+        // (Also prefetching the first image of the CTA that follows in this slot was measured and dropped: no gain, more registers.)
+        if (pf_rows > 0 && b + gridDim.z < (unsigned)B) {
+            // warp w issues rows w, w + 8, ... of every channel: addresses are warp-uniform (the bulk prefetch takes uniform
+            // registers; per-lane addresses made the compiler serialise the lanes in a loop)
+            const float* nimg = src + (size_t)(b + gridDim.z) * C * HW + blockIdx.x * kTileW;
+            const int r0 = (int)(blockIdx.y * kTileH) - (pf_rows - kTileH) / 2;
+            const unsigned bytes = (unsigned)min(kTileW, W - (int)(blockIdx.x * kTileW)) * 4u;
+            for (int c = 0; c < C; ++c, nimg += HW)
+                for (int rr = wid_u; rr < pf_rows; rr += 8) {
+                    const int r = r0 + rr;
+                    if ((unsigned)r < (unsigned)H)
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nimg + r * W), "r"(bytes) : "memory");
+                }
         }
         const float py0 = __fadd_rn(yf0, fy0), py1 = __fadd_rn(yf1, fy1);
         const float px0 = __fadd_rn(xf, fx0), px1 = __fadd_rn(xf, fx1);
@@ -199,112 +217,10 @@ __global__ void __launch_bounds__(256, MINB) warp2d_tile_kernel(const float* __r
     }
 }
 
-// ---- bilinear, tile STAGED through shared memory (C >= 2) ----
-// ncu of warp2d_tile_kernel at 300 x 5 x 224^2 (smooth flow): long scoreboard 11.6, issue 47 %, L1 55 %, DRAM 3.5 TB/s -- bound by the latency of its
-// scattered 4-byte gathers (8 per thread and channel in flight), not by a throughput.  Here the CTA first reduces the bounding box of
-// its 32 x 16 pixels' taps; when every tap is inside the image and the box fits, each channel's source patch is fetched with coalesced
-// 128-bit loads (every load of a channel in flight at once, the next channel's patch loading while this one is sampled) and the four
-// taps come from shared memory (consecutive lanes -> consecutive words for smooth flows).  Same coordinates, weights and ATen tap order
-// as the direct kernel: bit-identical output.  Any other tile (image border, flow pointing outside, wild flow) takes the direct path.
-constexpr int kSW = 64, kSH = 40;        // staged patch: up to 40 rows x 64 columns (tile 16 x 32 plus the flow's spread)
-
-template <bool FASTDIV>
-__global__ void __launch_bounds__(256, 5) warp2d_staged_kernel(const float* __restrict__ flow, const float* __restrict__ src,
-                                                                 float* __restrict__ out, int B, int C, int H, int W, float ry, float rx) {
-    __shared__ __align__(16) float patch[2][kSH * kSW];
-    __shared__ int box[8][4];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int x = blockIdx.x * kTileW + lane;
-    const int y = blockIdx.y * kTileH + wid * 2;
-    const bool act0 = x < W && y < H, act1 = x < W && y + 1 < H;
-    const unsigned HW = (unsigned)(H * W), pix = (unsigned)y * (unsigned)W + (unsigned)x;
-    const float s1y = (float)(H - 1), s1x = (float)(W - 1), hs1y = 0.5f * s1y, hs1x = 0.5f * s1x;
-    const float yf0 = (float)y, yf1 = (float)(y + 1), xf = (float)x;
-    float nfy0 = 0.f, nfy1 = 0.f, nfx0 = 0.f, nfx1 = 0.f;
-    if (blockIdx.z < (unsigned)B) {
-        const float* fyp = flow + ((size_t)blockIdx.z * 2) * HW + pix;
-        if (act0) { nfy0 = __ldcs(fyp); nfx0 = __ldcs(fyp + HW); }
-        if (act1) { nfy1 = __ldcs(fyp + W); nfx1 = __ldcs(fyp + HW + W); }
-    }
-    for (unsigned b = blockIdx.z; b < (unsigned)B; b += gridDim.z) {
-        const float fy0 = nfy0, fy1 = nfy1, fx0 = nfx0, fx1 = nfx1;
-        if (b + gridDim.z < (unsigned)B) {
-            const float* fyp = flow + ((size_t)(b + gridDim.z) * 2) * HW + pix;
-            if (act0) { nfy0 = __ldcs(fyp); nfx0 = __ldcs(fyp + HW); }
-            if (act1) { nfy1 = __ldcs(fyp + W); nfx1 = __ldcs(fyp + HW + W); }
-        }
-        const float py0 = __fadd_rn(yf0, fy0), py1 = __fadd_rn(yf1, fy1);
-        const float px0 = __fadd_rn(xf, fx0), px1 = __fadd_rn(xf, fx1);
-        bool ok = FASTDIV && fabsf(py0) < 16384.0f && fabsf(py1) < 16384.0f && fabsf(px0) < 16384.0f && fabsf(px1) < 16384.0f;
-        const float uy0 = warp_coord_lean(py0, s1y, ry, hs1y), uy1 = warp_coord_lean(py1, s1y, ry, hs1y);
-        const float ux0 = warp_coord_lean(px0, s1x, rx, hs1x), ux1 = warp_coord_lean(px1, s1x, rx, hs1x);
-        const float gy0 = floorf(uy0), gy1 = floorf(uy1), gx0 = floorf(ux0), gx1 = floorf(ux1);
-        const int iy0 = (int)gy0, iy1 = (int)gy1, ix0 = (int)gx0, ix1 = (int)gx1;
-        ok = ok && act1 && (unsigned)iy0 < (unsigned)(H - 1) && (unsigned)iy1 < (unsigned)(H - 1) &&
-             (unsigned)ix0 < (unsigned)(W - 1) && (unsigned)ix1 < (unsigned)(W - 1);
-        // bounding box of the CTA's taps (rows ymin .. ymax + 1, columns xmin .. xmax + 1)
-        {
-            const int wy0 = __reduce_min_sync(0xffffffffu, ok ? min(iy0, iy1) : -1), wy1 = __reduce_max_sync(0xffffffffu, max(iy0, iy1));
-            const int wx0 = __reduce_min_sync(0xffffffffu, ok ? min(ix0, ix1) : -1), wx1 = __reduce_max_sync(0xffffffffu, max(ix0, ix1));
-            __syncthreads();                      // the previous image's reads of `box` and of the patches are done
-            if (lane == 0) { box[wid][0] = wy0; box[wid][1] = wy1; box[wid][2] = wx0; box[wid][3] = wx1; }
-            __syncthreads();
-        }
-        int ymin = box[0][0], ymax = box[0][1], xmin = box[0][2], xmax = box[0][3];
-#pragma unroll
-        for (int k = 1; k < 8; ++k) {
-            ymin = min(ymin, box[k][0]); ymax = max(ymax, box[k][1]); xmin = min(xmin, box[k][2]); xmax = max(xmax, box[k][3]);
-        }
-        const int xs = xmin & ~3;                                  // 16-byte aligned first column of the patch
-        const int w4 = (xmax + 2 - xs + 3) >> 2, hn = ymax + 2 - ymin;     // patch: hn rows of w4 float4
-        const float* img = src + (size_t)b * C * HW;
-        float* o = out + (size_t)b * C * HW + pix;
-        if (ymin >= 0 && xmin >= 0 && hn <= kSH && w4 * 4 <= kSW) {     // CTA-uniform: every tap inside the image, the patch fits
-            const float ah0 = __fsub_rn(ux0, gx0), al0 = __fsub_rn(__fadd_rn(gx0, 1.0f), ux0);
-            const float bh0 = __fsub_rn(uy0, gy0), bl0 = __fsub_rn(__fadd_rn(gy0, 1.0f), uy0);
-            const float ah1 = __fsub_rn(ux1, gx1), al1 = __fsub_rn(__fadd_rn(gx1, 1.0f), ux1);
-            const float bh1 = __fsub_rn(uy1, gy1), bl1 = __fsub_rn(__fadd_rn(gy1, 1.0f), uy1);
-            const float w00a = __fmul_rn(al0, bl0), w01a = __fmul_rn(ah0, bl0), w10a = __fmul_rn(al0, bh0), w11a = __fmul_rn(ah0, bh0);
-            const float w00b = __fmul_rn(al1, bl1), w01b = __fmul_rn(ah1, bl1), w10b = __fmul_rn(al1, bh1), w11b = __fmul_rn(ah1, bh1);
-            const int oa = (iy0 - ymin) * kSW + (ix0 - xs), ob = (iy1 - ymin) * kSW + (ix1 - xs);
-            // loader role of this thread: two patch rows per warp pass, 16 float4 per row
-            const int lr = wid * 2 + (lane >> 4), lc = lane & 15;
-            const bool lcol = lc < w4;
-            const float* gsrc = img + (size_t)(ymin + lr) * W + xs + 4 * lc;
-            auto load_patch = [&](const float* chan, float* dst) {
-#pragma unroll
-                for (int k = 0; k < (kSH + 15) / 16; ++k) {
-                    const int r = lr + 16 * k;
-                    if (lcol && r < hn) {
-                        const float4 v = ldg_f4(chan + (size_t)(16 * k) * W);
-                        *reinterpret_cast<float4*>(dst + r * kSW + 4 * lc) = v;
-                    }
-                }
-            };
-            load_patch(gsrc, patch[0]);
-            for (int c = 0; c < C; ++c, o += HW) {
-                __syncthreads();                  // patch[c & 1] is complete; everybody has finished sampling patch[(c + 1) & 1]
-                if (c + 1 < C) load_patch(gsrc + (size_t)(c + 1) * HW, patch[(c + 1) & 1]);
-                const float* pa = patch[c & 1] + oa;
-                const float* pb = patch[c & 1] + ob;
-                float ra = __fmul_rn(pa[0], w00a);            // ATen order: nw, ne, sw, se
-                ra = fmaf(pa[1], w01a, ra);
-                ra = fmaf(pa[kSW], w10a, ra);
-                ra = fmaf(pa[kSW + 1], w11a, ra);
-                float rb = __fmul_rn(pb[0], w00b);
-                rb = fmaf(pb[1], w01b, rb);
-                rb = fmaf(pb[kSW], w10b, rb);
-                rb = fmaf(pb[kSW + 1], w11b, rb);
-                __stcs(o, ra);
-                __stcs(o + W, rb);
-            }
-        } else {
-            // direct path of this tile: the reference's sequence with per-tap bounds checks (as warp2d_tile_kernel's slow path)
-            if (act0) warp2d_general(img, o, C, H, W, py0, px0, ry, rx);
-            if (act1) warp2d_general(img, o + W, C, H, W, py1, px1, ry, rx);
-        }
-    }
-}
+// Measured and dropped (round 2, profiles/README.md "warp: staged patch"): staging each channel's source patch of the tile in shared
+// memory (bounding box of the CTA's taps, 16-byte cp.async, three images in flight per CTA, taps from LDS) is bit-identical but
+// slower at cfg3 C = 5: 237-325 us against 184-196 us for the direct gathers below -- the box of a 32 x 16 tile under a smooth 4-pixel
+// flow is about 22 x 46 words, the two patch sets cost the resident warps (4 CTAs per SM) and every image costs two CTA barriers.
 
 __global__ void __launch_bounds__(256) warp2d_taps_kernel(const float* __restrict__ flow, float* __restrict__ taps,
                                                           int H, int W, float ry, float rx, long total) {
@@ -481,18 +397,21 @@ int launch_warp2d(const float* flow, const float* src, int B, int C, int H, int 
     if (want == 0 && mode == CF_MODE_BILINEAR) {
         const int tiles_x = cdiv(W, kTileW), tiles_y = cdiv(H, kTileH);
         // a thread's setup (tile position, constants) is amortised over a few images once the grid fills the machine
-        static const int target = [] { const char* e = getenv("CF_WARP_CTAS"); return e ? atoi(e) : 2368; }();   // 148 SMs x 4 resident CTAs x 4 (measured: 1184 < 2368 ~ 4736)
+        static const int target = [] { const char* e = getenv("CF_WARP_CTAS"); return e ? atoi(e) : 9800; }();   // CTAs of about 3 images each; measured at cfg3 C = 5 (6 resident CTAs per SM): 882 CTAs 202 us, 2450 198, 4900 190, 9800 186, 14700 184, 29400 192; C = 1: 81 / 71 / 67 / 67 / 69 / 77
         long gz = (target + (long)tiles_x * tiles_y - 1) / ((long)tiles_x * tiles_y);
         gz = gz < 1 ? 1 : (gz > B ? B : (gz > 65535 ? 65535 : gz));
         const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)gz);
         if (tiles_y > 65535) return fail(CF_ERR_UNSUPPORTED, "warp2d: image height %d too large", H);
-        // several channels: stage each channel's source patch through shared memory (latency-bound gathers -> coalesced 128-bit loads);
-        // needs 16-byte aligned rows.  CF_WARP_STAGED = 0 / 1 forces the choice (A/B knob); default: C >= 2.
-        static const int staged_knob = [] { const char* e = getenv("CF_WARP_STAGED"); return e ? atoi(e) : -1; }();
-        const bool staged = (staged_knob < 0 ? C >= 2 : staged_knob != 0) && W % 4 == 0 && aligned16(src) && H - 1 <= 4095 && W - 1 <= 4095;
-        if (staged) warp2d_staged_kernel<true><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_);
-        else if (H - 1 <= 4095 && W - 1 <= 4095) warp2d_tile_kernel<true><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_);
-        else warp2d_tile_kernel<false><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_);
+        // L2 prefetch rows per tile and channel (0 = off); needs 16-byte aligned rows.  Measured at cfg3 (profiles/README.md, round 2
+        // "warp"): C = 5 175.5 us without, 173.5-174.5 with 16-24 rows (167 on another box); C = 1 69.0 without, 75 with: one channel
+        // issues on ~85 % of the cycles already and the prefetch instructions cost more than the latency they hide -> C >= 2 only.
+        static const int pf_knob = [] { const char* e = getenv("CF_WARP_PF"); return e ? atoi(e) : 16; }();
+        const int pf = (C >= 2 && W % 4 == 0 && aligned16(src)) ? pf_knob : 0;
+        // 8 resident CTAs per SM (32 registers, no spills) against 6 (40): C = 5 187.6 -> 175.5 us, C = 4 154.0 -> 144.8, C = 1 69.0 = 69.0
+        static const int minb8 = [] { const char* e = getenv("CF_WARP_MINB8"); return e ? atoi(e) : 1; }();
+        if (H - 1 <= 4095 && W - 1 <= 4095 && minb8) warp2d_tile_kernel<true, 1, 8><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_, pf);
+        else if (H - 1 <= 4095 && W - 1 <= 4095) warp2d_tile_kernel<true><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_, pf);
+        else warp2d_tile_kernel<false><<<grid, 256, 0, s>>>(flow, src, out, B, C, H, W, ry_, rx_, pf);
         CF_CHECK_LAUNCH("warp2d_tile_kernel");
         return CF_OK;
     }

@@ -1,5 +1,7 @@
 #!/bin/bash
-mkdir -p gpurun_out/c17
-timeout 300 python tools/kbench.py cfg4 --only otf --reps 6 > gpurun_out/c17/plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:lookup_tc -s 2 -c 1 -o gpurun_out/c17/ltc python tools/kbench.py cfg4 --only otf --reps 6 > gpurun_out/c17/ncu2.log 2>&1
-tail -n 2 gpurun_out/c17/ncu2.log
+mkdir -p gpurun_out; rm -f gpurun_out/c17.log
+for t in 4900 7350 9800 14700 29400; do
+  echo "== staged=0 target=$t" >> gpurun_out/c17.log
+  CF_WARP_STAGED=0 CF_WARP_CTAS=$t timeout 300 python tools/kbench.py cfg3 --graph --only warp 2>&1 | grep -E "warp 300x" >> gpurun_out/c17.log
+done
+cat gpurun_out/c17.log

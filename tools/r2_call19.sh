@@ -1,12 +1,8 @@
 #!/bin/bash
-mkdir -p gpurun_out/c19
-CF_BF16_W32_V1=0 timeout 600 python -m pytest tests/test_gpu_build_v2.py tests/test_gpu_corr.py -x -q -m gpu > gpurun_out/c19/pytest.log 2>&1
-tail -n 4 gpurun_out/c19/pytest.log
-for nb in 1 2; do
-  echo "== NB=$nb" >> gpurun_out/c19/sweep.log
-  CF_TC2_NB=$nb CF_BF16_W32_V1=0 SW_P=29,116 SW_PREC=bf16 timeout 300 python tools/build_sweep.py >> gpurun_out/c19/sweep.log 2>&1
-  CF_TC2_NB=$nb SW_HW=64 SW_P=64 SW_PREC=bf16 timeout 300 python tools/build_sweep.py >> gpurun_out/c19/sweep.log 2>&1
-done
-echo "== v1" >> gpurun_out/c19/sweep.log
-SW_P=29,116 SW_PREC=bf16 timeout 300 python tools/build_sweep.py >> gpurun_out/c19/sweep.log 2>&1
-grep -E "==|build_sweep" gpurun_out/c19/sweep.log
+mkdir -p gpurun_out; rm -f gpurun_out/c19.log
+timeout 600 python -m pytest tests/test_gpu_warp.py -m gpu -x -q 2>&1 | tail -n 2 >> gpurun_out/c19.log
+for m in 0 1; do for pf in 0 16; do
+  echo "== minb8=$m pf=$pf" >> gpurun_out/c19.log
+  CF_WARP_MINB8=$m CF_WARP_PF=$pf timeout 300 python tools/kbench.py cfg3 --graph --only warp 2>&1 | grep -E "warp 300x" >> gpurun_out/c19.log
+done; done
+cat gpurun_out/c19.log

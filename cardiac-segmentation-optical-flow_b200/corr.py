@@ -121,9 +121,18 @@ class _CorrBuild(torch.autograd.Function):
         with torch.cuda.device(f1.device):
             s = _cabi.stream()
             _cabi.check(lib.cf_corr_pool_bwd(g.data_ptr(), B, H, W, L, s), "cf_corr_pool_bwd")
-            _cabi.check(lib.cf_corr_volume_bwd(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W,
-                                               gf1.data_ptr(), gf2.data_ptr(), s), "cf_corr_volume_bwd")
-        return gf1, gf2, None, None, None, None, None, None
+            # fp32 forward -> fp32 CUDA-core GEMMs; bf16 / bf16x3 forward -> tcgen05 with the bf16x3 split (fp32-grade) where
+            # the shape allows it (H*W % 8 == 0), reported in used
+            prec = _cabi.PRECISIONS["fp32"] if ctx.used_precision == _cabi.PRECISIONS["fp32"] else _cabi.PRECISIONS["auto"]
+            ws_bytes = lib.cf_corr_volume_bwd_workspace_bytes(B, C, H, W) if prec != _cabi.PRECISIONS["fp32"] else 0
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=f1.device) if ws_bytes else None
+            used = _cabi.ctypes.c_int(0)
+            _cabi.check(lib.cf_corr_volume_bwd_ex(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W, prec,
+                                                  gf1.data_ptr() if ctx.needs_input_grad[0] else None,
+                                                  gf2.data_ptr() if ctx.needs_input_grad[1] else None,
+                                                  ws.data_ptr() if ws is not None else None, ws_bytes,
+                                                  _cabi.ctypes.byref(used), s), "cf_corr_volume_bwd_ex")
+        return (gf1 if ctx.needs_input_grad[0] else None), (gf2 if ctx.needs_input_grad[1] else None), None, None, None, None, None, None
 
 
 class _CorrLookup(torch.autograd.Function):

@@ -346,6 +346,30 @@ int cf_corr_volume_bwd(const float* f1, const float* f2, const float* grad_corr,
     return launch_corr_volume_bwd(f1, f2, grad_corr, B, C, H * W, grad_f1, grad_f2, (cudaStream_t)stream);
 }
 
+size_t cf_corr_volume_bwd_workspace_bytes(int B, int C, int H, int W) {
+    if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || !corr_bwd_tc_supported(B, C, H * W)) return 0;
+    return corr_bwd_tc_workspace_bytes(B, C, H * W);
+}
+
+int cf_corr_volume_bwd_ex(const float* f1, const float* f2, const float* grad_corr, int B, int C, int H, int W, int precision,
+                          float* grad_f1, float* grad_f2, void* workspace, size_t workspace_bytes, int* used_precision,
+                          void* stream) {
+    CF_REQUIRE(f1 && f2 && grad_corr, CF_ERR_BAD_ARG, "cf_corr_volume_bwd_ex: null pointer");
+    CF_REQUIRE(grad_f1 || grad_f2, CF_ERR_BAD_ARG, "cf_corr_volume_bwd_ex: neither grad_f1 nor grad_f2 requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_corr_volume_bwd_ex: bad shape");
+    CF_REQUIRE(precision == CF_PREC_AUTO || precision == CF_PREC_FP32 || precision == CF_PREC_BF16X3, CF_ERR_BAD_ARG,
+               "cf_corr_volume_bwd_ex: precision %d (auto, fp32 or bf16x3)", precision);
+    const bool tc_ok = corr_bwd_tc_supported(B, C, H * W);
+    if (precision == CF_PREC_BF16X3 && !tc_ok)
+        return fail(CF_ERR_UNSUPPORTED, "cf_corr_volume_bwd_ex: bf16x3 needs H*W %% 8 == 0 and a driver with tensor-map encoding");
+    const bool use_tc = precision != CF_PREC_FP32 && tc_ok;
+    if (used_precision) *used_precision = use_tc ? CF_PREC_BF16X3 : CF_PREC_FP32;
+    if (use_tc)
+        return launch_corr_volume_bwd_tc(f1, f2, grad_corr, B, C, H * W, grad_f1, grad_f2, workspace, workspace_bytes,
+                                         (cudaStream_t)stream);
+    return launch_corr_volume_bwd(f1, f2, grad_corr, B, C, H * W, grad_f1, grad_f2, (cudaStream_t)stream);
+}
+
 int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream) {
     CF_REQUIRE(vec && out, CF_ERR_BAD_ARG, "cf_vecint: null pointer");
     CF_REQUIRE(B > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_vecint: bad shape B=%d H=%d W=%d", B, H, W);

@@ -135,7 +135,7 @@ int make_tmap_bf16(CUtensorMap* m, const void* ptr, int rank, const uint64_t* di
 int launch_prep_transpose_one(const float* src, void* dst_bf16, int B, int C, int HW, cudaStream_t s);
 // multiprocessor count of the current device (cached per device)
 int sm_count();
-// opt a kernel in to `bytes` of dynamic shared memory on the current device, once per (device, slot < 32); slots: corr_tc2 0-2, lookup_tc 5-8, corr_tcgen05 16-17, lookup_fused 21-24
+// opt a kernel in to `bytes` of dynamic shared memory on the current device, once per (device, slot < 32); slots: corr_tc2 0-2, lookup_tc 5-8, corr_bwd_tc 12, corr_tcgen05 16-17, lookup_fused 21-24
 int smem_optin(const void* func, size_t bytes, int slot);
 
 }  // namespace cf

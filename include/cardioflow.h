@@ -188,6 +188,16 @@ CF_API int cf_corr_pool_bwd(float* grad_pyramid, int B, int H, int W, int L, voi
 CF_API int cf_corr_volume_bwd(const float* f1, const float* f2, const float* grad_corr /* level 0 */, int B, int C,
                        int H, int W, float* grad_f1, float* grad_f2, void* stream);
 
+/* The same two products on the tensor cores (tcgen05, fp32-grade through the bf16x3 split: |error| <= ~1e-5 of the result's scale;
+ * corr_bwd_tc.cu).  precision: CF_PREC_AUTO (tensor cores when H*W % 8 == 0, else the fp32 CUDA-core GEMMs), CF_PREC_FP32,
+ * CF_PREC_BF16X3 (error when unsupported).  workspace: cf_corr_volume_bwd_workspace_bytes (0 = the tensor-core path does not
+ * apply), 256-byte aligned device memory.  *used_precision reports the path taken.  Reference: autograd through
+ * SegFlowGaussian.py:929-935 (training loop SegFlowGaussian.py:2225 of network_training). */
+CF_API size_t cf_corr_volume_bwd_workspace_bytes(int B, int C, int H, int W);
+CF_API int cf_corr_volume_bwd_ex(const float* f1, const float* f2, const float* grad_corr /* level 0 */, int B, int C, int H, int W,
+                          int precision, float* grad_f1 /* may be NULL */, float* grad_f2 /* may be NULL */, void* workspace,
+                          size_t workspace_bytes, int* used_precision /* may be NULL */, void* stream);
+
 /* VecInt (integration.py:82-99): vec/2^n then n x (vec += warp(vec, vec)); work = scratch [B,2,H,W]. */
 CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream);
 

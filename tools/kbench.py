@@ -165,7 +165,19 @@ if args.cfg in ("cfg2", "cfg4", "cfg1") and want("bwd"):
     gf1, gf2 = torch.empty_like(f1[0]), torch.empty_like(f2[0])
     us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_volume_bwd(f1[i].data_ptr(), f2[i].data_ptr(), gp[i].data_ptr(), P, C, H, W,
                                                                   gf1.data_ptr(), gf2.data_ptr(), st_())), nrot, reps=max(5, args.reps // 4))
-    report("corr volume backward (2 GEMMs)", us, mn, P * (4 * HWn * HWn + 16 * C * HWn), 4.0 * P * HWn * HWn * C)
+    report("corr volume backward (2 GEMMs), fp32 CUDA cores", us, mn, P * (4 * HWn * HWn + 16 * C * HWn), 4.0 * P * HWn * HWn * C)
+    wsb = lib.cf_corr_volume_bwd_workspace_bytes(P, C, H, W)
+    if wsb:
+        import ctypes
+        wsv = torch.empty(wsb, dtype=torch.uint8, device=dev)
+        usedp = ctypes.c_int(0)
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_volume_bwd_ex(f1[i].data_ptr(), f2[i].data_ptr(), gp[i].data_ptr(), P, C, H, W,
+                                                                         _cabi.PRECISIONS["auto"], gf1.data_ptr(), gf2.data_ptr(), wsv.data_ptr(), wsb,
+                                                                         ctypes.byref(usedp), st_())), nrot, reps=max(5, args.reps // 4))
+        # G is read once per product (2 x 4 HW^2), the maps are read and the gradients written
+        report(f"corr volume backward (2 GEMMs), tcgen05 {_cabi.PRECISION_NAMES.get(usedp.value, usedp.value)}", us, mn,
+               P * (8 * HWn * HWn + 16 * C * HWn), 4.0 * P * HWn * HWn * C)
+        del wsv
     for cin in (1, 5):
         img = [torch.rand(P, cin, IH, IH, device=dev) for _ in range(nrot)]
         flow = [torch.randn(P, 2, IH, IH, device=dev) * 3 for _ in range(nrot)]

@@ -45,23 +45,25 @@ struct BwdMaps {
 
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// 8 floats -> 8 bf16 hi (x rounded) + 8 bf16 lo (x - hi rounded), packed in K order.  Two values per step: one packed convert
+// for hi, a shift / mask to get hi back as floats, two subtractions, one packed convert for lo.
 __device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
     uint32_t h[4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * i]), h1 = __float2bfloat16_rn(v[2 * i + 1]);
-        const __nv_bfloat16 l0 = __float2bfloat16_rn(__fsub_rn(v[2 * i], __bfloat162float(h0)));
-        const __nv_bfloat16 l1 = __float2bfloat16_rn(__fsub_rn(v[2 * i + 1], __bfloat162float(h1)));
-        h[i] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-        l[i] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+        const __nv_bfloat162 hp = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);      // .x (low half) = the lower K index
+        h[i] = *reinterpret_cast<const uint32_t*>(&hp);
+        const float h0 = __uint_as_float(h[i] << 16), h1 = __uint_as_float(h[i] & 0xffff0000u);
+        const __nv_bfloat162 lp = __floats2bfloat162_rn(__fsub_rn(v[2 * i], h0), __fsub_rn(v[2 * i + 1], h1));
+        l[i] = *reinterpret_cast<const uint32_t*>(&lp);
     }
     hi = make_uint4(h[0], h[1], h[2], h[3]);
     lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-__global__ void __launch_bounds__(NTHREADS, 1) corr_bwd_tc_kernel(const __grid_constant__ BwdMaps M, const BwdParams P) {
-    extern __shared__ uint8_t smem_raw[];
-    __shared__ uint32_t tmem_base_slot;
+template <int GEMM>      // 0: gf1 (rows p, K = q); 1: gf2 (rows q, K = p): one specialised body per product, chosen per CTA
+__device__ __forceinline__ void corr_bwd_tc_body(const BwdMaps& M, const BwdParams& P, uint8_t* smem_raw, uint32_t& tmem_base_slot,
+                                                 int tile) {
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* const gen = smem_raw + (base - smem_u32(smem_raw));
     const uint32_t s_bars = base + (uint32_t)NSTAGE * STAGE_BYTES;
@@ -69,10 +71,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_bwd_tc_kernel(const __grid_c
     auto bar = [&](int i) { return s_bars + 8u * (uint32_t)i; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int slot = (int)blockIdx.x / (P.n_tiles * P.m_tiles);
-    const int rem = (int)blockIdx.x - slot * (P.n_tiles * P.m_tiles);
-    const int mt = rem / P.n_tiles, nt = rem - mt * P.n_tiles;
-    const int gemm = P.gemm_of[slot];
+    const int mt = tile / P.n_tiles, nt = tile - mt * P.n_tiles;
+    constexpr int gemm = GEMM;
     const int b = (int)blockIdx.y;
     const int m0 = mt * BM, n0 = nt * BN;
     const int HW = P.HW, KB = P.k_blocks;
@@ -133,6 +133,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_bwd_tc_kernel(const __grid_c
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
     }
+}
+
+// One launch covers both products (grid.x = slots x tiles): 928 CTAs = 6.3 waves at cfg2 instead of two launches of 3.1 waves each.
+__global__ void __launch_bounds__(NTHREADS, 1) corr_bwd_tc_kernel(const __grid_constant__ BwdMaps M, const BwdParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint32_t tmem_base_slot;
+    const int tiles = P.m_tiles * P.n_tiles;
+    const int slot = (int)blockIdx.x / tiles, tile = (int)blockIdx.x - slot * tiles;
+    if (P.gemm_of[slot] == 0) corr_bwd_tc_body<0>(M, P, smem_raw, tmem_base_slot, tile);
+    else corr_bwd_tc_body<1>(M, P, smem_raw, tmem_base_slot, tile);
 }
 
 // fp32 -> bf16 hi / lo planes, same [B, C, HW] layout

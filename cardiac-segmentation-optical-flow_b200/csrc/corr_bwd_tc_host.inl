@@ -49,9 +49,6 @@ int launch_corr_volume_bwd_tc(const float* f1, const float* f2, const float* g, 
     P.g = g;
     P.out[0] = gf1;
     P.out[1] = gf2;
-    int slots = 0;
-    if (gf1) P.gemm_of[slots++] = 0;
-    if (gf2) P.gemm_of[slots++] = 1;
     P.B = B;
     P.C = C;
     P.HW = HW;
@@ -59,6 +56,9 @@ int launch_corr_volume_bwd_tc(const float* f1, const float* f2, const float* g, 
     P.m_tiles = cdiv(HW, BM);
     P.n_tiles = cdiv(C, BN);
     P.div = sqrtf((float)C);
+    int slots = 0;
+    if (gf1) P.gemm_of[slots++] = 0;
+    if (gf2) P.gemm_of[slots++] = 1;
     const long gx = (long)slots * P.m_tiles * P.n_tiles;
     if (gx > 0x7fffffffL) return fail(CF_ERR_UNSUPPORTED, "corr_volume_bwd (tensor cores): grid too large");
     if (int rc = smem_optin(reinterpret_cast<const void*>(&corr_bwd_tc_kernel), kSmemBytes, 12)) return rc;

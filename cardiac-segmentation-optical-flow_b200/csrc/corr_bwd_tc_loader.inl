@@ -25,13 +25,14 @@
                 }
             } else {
                 const int m = m0 + tl;
+                const bool row_in = m < HW;
+                const float* src = gb + (size_t)k0 * HW + m;
+                const unsigned uHW = (unsigned)HW;               // element offsets inside one pair's G fit 32 bits (HW <= 65535)
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const int k = k0 + 8 * i;
-                    const bool in = m < HW && k < HW;
-                    const float* src = gb + (size_t)k * HW + m;
+                    const bool in = row_in && k0 + 8 * i < HW;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) v[8 * i + j] = in ? __ldg(src + (size_t)j * HW) : 0.0f;
+                    for (int j = 0; j < 8; ++j) v[8 * i + j] = in ? __ldg(src + (unsigned)(8 * i + j) * uHW) : 0.0f;
                 }
             }
         };

@@ -163,9 +163,10 @@ if args.cfg in ("cfg2", "cfg4", "cfg1") and want("bwd"):
     lv = [(H >> k) * (W >> k) for k in range(L)]
     report("pool chain backward", us, mn, P * HWn * 4 * (2 * lv[0] + 2 * lv[1] + 2 * lv[2] + lv[3]))
     gf1, gf2 = torch.empty_like(f1[0]), torch.empty_like(f2[0])
-    us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_volume_bwd(f1[i].data_ptr(), f2[i].data_ptr(), gp[i].data_ptr(), P, C, H, W,
-                                                                  gf1.data_ptr(), gf2.data_ptr(), st_())), nrot, reps=max(5, args.reps // 4))
-    report("corr volume backward (2 GEMMs), fp32 CUDA cores", us, mn, P * (4 * HWn * HWn + 16 * C * HWn), 4.0 * P * HWn * HWn * C)
+    if not os.environ.get("KB_SKIP_SIMT_BWD"):
+        us, mn = timeit(lambda i: _cabi.check(lib.cf_corr_volume_bwd(f1[i].data_ptr(), f2[i].data_ptr(), gp[i].data_ptr(), P, C, H, W,
+                                                                      gf1.data_ptr(), gf2.data_ptr(), st_())), nrot, reps=max(5, args.reps // 4))
+        report("corr volume backward (2 GEMMs), fp32 CUDA cores", us, mn, P * (4 * HWn * HWn + 16 * C * HWn), 4.0 * P * HWn * HWn * C)
     wsb = lib.cf_corr_volume_bwd_workspace_bytes(P, C, H, W)
     if wsb:
         import ctypes

@@ -55,7 +55,7 @@ int check_corr_shape(int B, int H, int W, int L, LevelDims* d) {
 using namespace cf;
 
 #ifdef CF_BRINGUP
-namespace cf { void corr_tcgen05_set_debug(float* p); void corr_tcgen05_set_timestamps(unsigned long long* p, int cta); }
+namespace cf { void corr_tcgen05_set_debug(float* p); void corr_tcgen05_set_timestamps(unsigned long long* p, int cta); void lookup_set_timestamps(unsigned long long* p); }
 #endif
 
 extern "C" {
@@ -63,6 +63,7 @@ extern "C" {
 #ifdef CF_BRINGUP   // bring-up hooks (CF_NVCC_EXTRA=-DCF_BRINGUP): not in the public header, not in the shipped library
 CF_API void cf_debug_set_gemm_dump(float* p) { cf::corr_tcgen05_set_debug(p); }
 CF_API void cf_debug_set_gemm_timestamps(unsigned long long* p, int cta) { cf::corr_tcgen05_set_timestamps(p, cta); }
+CF_API void cf_debug_set_lookup_timestamps(unsigned long long* p) { cf::lookup_set_timestamps(p); }
 #endif
 
 int cf_version(void) { return 100; }

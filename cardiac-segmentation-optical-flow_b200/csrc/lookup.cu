@@ -32,9 +32,29 @@ namespace {
 
 constexpr int kQT = 32;  // queries per CTA
 
+#ifdef CF_BRINGUP   // per-CTA phase timeline (tools/lookup_ts.py); not in the shipped build
+__device__ unsigned long long* g_lookup_ts = nullptr;
+__device__ __forceinline__ void ts_stamp(int slot, float dep = 0.0f) {
+    if (g_lookup_ts && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "f"(dep) : "memory");
+        g_lookup_ts[(size_t)blockIdx.x * 8 + slot] = t;
+        if (slot == 0) {
+            unsigned sm;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+            g_lookup_ts[(size_t)blockIdx.x * 8 + 7] = sm;
+        }
+    }
+}
+#define CF_TS(slot, dep) ts_stamp(slot, dep)
+#else
+#define CF_TS(slot, dep)
+#endif
+
 // Window geometry.  The round trip moves a coordinate by far less than 0.5, so the floors of a query's taps can only
-// flip DOWN when frac(c) < 0.5 and only UP otherwise: anchoring the window at floor(c) - r - (frac < 0.5) makes
-// 2r+3 rows / columns enough for every case (nominal taps: 2r+2).
+// flip DOWN when frac(c) < 0.5 and only UP otherwise: anchoring the window of a query that can flip at
+// floor(c) - r - (frac < 0.5) makes 2r+3 rows / columns enough for every case; a nominal query (no flip possible) is
+// anchored at floor(c) - r and uses the first 2r+2.
 template <int R>
 struct Geo {
     static constexpr int SIDE = 2 * R + 1;
@@ -44,7 +64,7 @@ struct Geo {
     static constexpr int QP = PR * PC + (((PR * PC / 4) % 2 == 0) ? 4 : 0);   // words per query: QP / 4 odd
     static_assert(QP % 4 == 0 && (QP / 4) % 2 == 1, "window pitch / 4 must be odd");
     static constexpr int WIN = kQT * QP + 16;            // + the 16 B skews of win_base()
-    static constexpr int XT = SIDE * 3 * kQT;            // shared x taps: [SIDE][window column, w_lo, w_hi][query]
+    static constexpr int XT = SIDE * 3 * kQT;            // shared x taps: [SIDE][query] (w_lo, w_hi) pairs, then [SIDE][query] window columns
     static constexpr size_t SMEM = (size_t)(WIN + XT) * sizeof(float);
 };
 
@@ -122,19 +142,20 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
     const int qq = lane >> 2, ch = lane & 3;
     const int img_words = hl * wl;
     const uint64_t pol = l2_evict_last_policy(l2_frac);
-    // Owner side, once per lane: which of the 4 chunks its query's taps can read (nominal = the 2r+2 columns from
-    // (lo ? 1 : 0), else all PR) and the one row only a flipped floor can reach, packed for the staging lanes:
+    // Owner side, once per lane: which of the 4 chunks its query's taps can read (nominal = the first 2r+2 columns,
+    // else all PR) and the one row only a flipped floor can reach, packed for the staging lanes:
     // bit 0 dead, bits 1-4 chunk needed, bits 5-8 skipped window row (15 = none)
     unsigned info;
     {
+        // a nominal query's window is anchored AT its first tap (columns / rows 0 .. 2r+1); only a query whose floors can flip
+        // needs the extra column / row
         const int osh = VEC ? (ax & 3) : 0;
-        const int c0 = (flags & kNomX) ? ((flags & kLoX) ? 1 : 0) : 0;
-        const int c1 = (flags & kNomX) ? c0 + 2 * R + 1 : PR - 1;
+        const int c1 = (flags & kNomX) ? 2 * R + 1 : PR - 1;
         unsigned need = 0;
 #pragma unroll
         for (int c = 0; c < 4; ++c)
-            if ((4 * c + 3 >= osh + c0) && (4 * c <= osh + c1) && (4 * c < PC)) need |= 1u << c;
-        const unsigned oskip = (flags & kNomY) ? ((flags & kLoY) ? 0u : (unsigned)(PR - 1)) : 15u;
+            if ((4 * c <= osh + c1) && (4 * c < PC)) need |= 1u << c;
+        const unsigned oskip = (flags & kNomY) ? (unsigned)(PR - 1) : 15u;
         info = ((flags & kDead) ? 1u : 0u) | (need << 1) | (oskip << 5);
     }
 #pragma unroll
@@ -184,12 +205,14 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     constexpr int JPW = (SIDE + NW - 1) / NW;   // output rows (and taps per axis) per warp
     extern __shared__ __align__(16) float smem[];
     float* const win = smem;                    // windows: win_base(q) + row * PC + column
-    float* const xt = smem + G::WIN;            // [SIDE][3][kQT]: x taps (window column, w_lo, w_hi)
+    float2* const xw = reinterpret_cast<float2*>(smem + G::WIN);   // [SIDE][kQT]: x tap weights (w_lo, w_hi)
+    int* const xc = reinterpret_cast<int*>(smem + G::WIN + 2 * SIDE * kQT);   // [SIDE][kQT]: x tap window column
 
     // Programmatic dependent launch: let the NEXT kernel of the stream (normally the next lookup) be scheduled while this
     // grid drains -- its CTAs become resident and run their index arithmetic, then block in griddepcontrol.wait below
     // until this grid has completed and flushed.  No effect on launches made without the PDL attribute.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    CF_TS(0, 0.0f);
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     // levels interleave in launch order (read-heavy fine levels next to store-heavy coarse ones)
     const unsigned task = P.lshift >= 0 ? (blockIdx.x >> P.lshift) : blockIdx.x / (unsigned)P.L;
@@ -215,13 +238,17 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
         cy = __fmul_rn(__ldg(cp + P.HW), inv);
     }
     // every tap of a query this far out is outside any image -> zeros (also catches NaN / inf)
+    CF_TS(1, cx + cy);
     const bool dead = !valid || !(fabsf(cx) < kDeadCoord) || !(fabsf(cy) < kDeadCoord);
     bool nom_x, nom_y, lo_x, lo_y;
     classify<R>(cx, wl, nom_x, lo_x);
     classify<R>(cy, hl, nom_y, lo_y);
-    // window anchor: first nominal tap, minus one when floors can flip down
-    const int ax = dead ? 0 : __float2int_rd(cx) - R - (lo_x ? 1 : 0);
-    const int ay = dead ? 0 : __float2int_rd(cy) - R - (lo_y ? 1 : 0);
+    // window anchor: the first nominal tap -- minus one only for a query whose floors can actually flip down.  Nominal queries
+    // (all of them on the fast path) then read their taps at the same window rows / columns up to the alignment shift `sh`:
+    // with the anchor always one lower for frac < 0.5 the per-lane read offset took 10 values instead of 4 and the shared-memory
+    // reads of a warp collided 3.8-fold (ncu: 47 % of the wavefronts were bank-conflict replays; the kernel is LSU-bound)
+    const int ax = dead ? 0 : __float2int_rd(cx) - R - ((!nom_x && lo_x) ? 1 : 0);
+    const int ay = dead ? 0 : __float2int_rd(cy) - R - ((!nom_y && lo_y) ? 1 : 0);
     const int sh = vec ? (ax & 3) : 0;             // stored column of the anchor
     const bool fast = __all_sync(0xffffffffu, dead || (nom_x && nom_y));
 
@@ -236,6 +263,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
         else stage_windows<R, NW, false>(win_s, img0, hl, wl, w, lane, ax, ay, flags, P.l2_frac);
     }
 
+    CF_TS(2, 0.0f);
     // taps: warp w computes taps w*JPW.. of both axes; x taps are shared, y taps stay in registers
     int yoff[JPW];
     float ywl[JPW], ywh[JPW];
@@ -250,16 +278,17 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
                 int i0;
                 float lo, hi;
                 axis_tap(cx, t - R, s1x, rx, i0, lo, hi);
-                xt[(t * 3 + 0) * kQT + lane] = __int_as_float(min(max(i0 - ax, 0), PR - 2) + sh);
-                xt[(t * 3 + 1) * kQT + lane] = lo;
-                xt[(t * 3 + 2) * kQT + lane] = hi;
+                xc[t * kQT + lane] = min(max(i0 - ax, 0), PR - 2) + sh;
+                xw[t * kQT + lane] = make_float2(lo, hi);
                 axis_tap(cy, t - R, s1y, ry, i0, ywl[k], ywh[k]);
                 yoff[k] = min(max(i0 - ay, 0), PR - 2) * PC;
             }
         }
     }
+    CF_TS(3, ywl[0]);
     cp_async_wait_all();
     __syncthreads();
+    CF_TS(4, 0.0f);
 
     // ---- (2r+1) x JPW outputs per lane, channel-major stores (128 B per warp per channel) ----
     if (!valid) return;
@@ -283,23 +312,63 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
         return;
     }
     if (fast) {
-        // nominal taps: with o = (lo ? 1 : 0), x tap i reads stored columns sh+o+i, +1; output row j reads rows o+j, +1
-        const float* rp = sq + (j0 + (lo_y ? 1 : 0)) * PC + sh + (lo_x ? 1 : 0);
-        float r[JPW + 1][SIDE + 1];
+        // nominal taps: x tap i reads stored columns sh+i, +1; output row j reads window rows j, +1.
+        // The kernel issues on 63 % of the cycles (ncu), a fifth of them these blends: two output rows are blended at once with the
+        // packed fp32 instructions of sm_100 (FMUL2 / FFMA2: IEEE round-to-nearest per component, so every output keeps the exact
+        // sequence fmul, fma, fma, fma in ATen's nw, ne, sw, se order).  Pair kp = rows (2kp, 2kp+1): top[c] = (r[2kp][c], r[2kp+1][c]),
+        // bot[c] = (r[2kp+1][c], r[2kp+2][c]); an odd last row runs the scalar sequence with packed weight products.
+        constexpr int NP = JPW / 2;
+        constexpr bool ODD = (JPW & 1) != 0;
+        const float* rp = sq + j0 * PC + sh;
+        float2 top[NP > 0 ? NP : 1][SIDE + 1], bot[NP > 0 ? NP : 1][SIDE + 1], yl2[NP > 0 ? NP : 1], yh2[NP > 0 ? NP : 1];
+        float s0[SIDE + 1], s1[SIDE + 1];            // odd last row: its two window rows
 #pragma unroll
-        for (int k = 0; k <= JPW; ++k)
+        for (int kp = 0; kp < NP; ++kp) {
+            const int k = 2 * kp;
+            yl2[kp] = make_float2(ywl[k], ywl[k + 1]);
+            yh2[kp] = make_float2(ywh[k], ywh[k + 1]);
 #pragma unroll
-            for (int c = 0; c <= SIDE; ++c) r[k][c] = (j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f;
+            for (int c = 0; c <= SIDE; ++c) {
+                const float r0 = (j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f;
+                const float r1 = (j0 + k + 1 <= SIDE) ? rp[(k + 1) * PC + c] : 0.0f;
+                const float r2 = (j0 + k + 2 <= SIDE) ? rp[(k + 2) * PC + c] : 0.0f;
+                top[kp][c] = make_float2(r0, r1);
+                bot[kp][c] = make_float2(r1, r2);
+            }
+        }
+        if (ODD) {
+            constexpr int k = JPW - 1;
+#pragma unroll
+            for (int c = 0; c <= SIDE; ++c) {
+                s0[c] = NP > 0 ? bot[NP > 0 ? NP - 1 : 0][c].y : ((j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f);
+                s1[c] = (j0 + k + 1 <= SIDE) ? rp[(k + 1) * PC + c] : 0.0f;
+            }
+        }
 #pragma unroll
         for (int i = 0; i < SIDE; ++i) {
-            const float xl = xt[(i * 3 + 1) * kQT + lane], xh = xt[(i * 3 + 2) * kQT + lane];
+            const float2 x = xw[i * kQT + lane];                  // (w_lo, w_hi) of x tap i
+            const float2 xll = make_float2(x.x, x.x), xhh = make_float2(x.y, x.y);
 #pragma unroll
-            for (int k = 0; k < JPW; ++k) {
+            for (int kp = 0; kp < NP; ++kp) {
+                const int k = 2 * kp;
                 if (j0 + k < SIDE) {
-                    float acc = __fmul_rn(r[k][i], __fmul_rn(xl, ywl[k]));
-                    acc = fmaf(r[k][i + 1], __fmul_rn(xh, ywl[k]), acc);
-                    acc = fmaf(r[k + 1][i], __fmul_rn(xl, ywh[k]), acc);
-                    acc = fmaf(r[k + 1][i + 1], __fmul_rn(xh, ywh[k]), acc);
+                    float2 acc = __fmul2_rn(top[kp][i], __fmul2_rn(xll, yl2[kp]));
+                    acc = __ffma2_rn(top[kp][i + 1], __fmul2_rn(xhh, yl2[kp]), acc);
+                    acc = __ffma2_rn(bot[kp][i], __fmul2_rn(xll, yh2[kp]), acc);
+                    acc = __ffma2_rn(bot[kp][i + 1], __fmul2_rn(xhh, yh2[kp]), acc);
+                    __stcs(reinterpret_cast<float*>(ok[k]), acc.x);
+                    ok[k] += ostep;
+                    if (j0 + k + 1 < SIDE) { __stcs(reinterpret_cast<float*>(ok[k + 1]), acc.y); ok[k + 1] += ostep; }
+                }
+            }
+            if (ODD) {
+                constexpr int k = JPW - 1;
+                if (j0 + k < SIDE) {
+                    const float2 wl2 = __fmul2_rn(x, make_float2(ywl[k], ywl[k])), wh2 = __fmul2_rn(x, make_float2(ywh[k], ywh[k]));
+                    float acc = __fmul_rn(s0[i], wl2.x);
+                    acc = fmaf(s0[i + 1], wl2.y, acc);
+                    acc = fmaf(s1[i], wh2.x, acc);
+                    acc = fmaf(s1[i + 1], wh2.y, acc);
                     __stcs(reinterpret_cast<float*>(ok[k]), acc);
                     ok[k] += ostep;
                 }
@@ -308,8 +377,9 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     } else {
 #pragma unroll
         for (int i = 0; i < SIDE; ++i) {
-            const int xo = __float_as_int(xt[(i * 3 + 0) * kQT + lane]);
-            const float xl = xt[(i * 3 + 1) * kQT + lane], xh = xt[(i * 3 + 2) * kQT + lane];
+            const int xo = xc[i * kQT + lane];
+            const float2 x = xw[i * kQT + lane];
+            const float xl = x.x, xh = x.y;
 #pragma unroll
             for (int k = 0; k < JPW; ++k) {
                 if (j0 + k < SIDE) {
@@ -324,6 +394,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
             }
         }
     }
+    CF_TS(5, 0.0f);
 }
 
 // Variant: ONE warp per CTA owns 32 queries x one level and evaluates all (2r+1)^2 outputs of its queries.  Nothing is
@@ -360,8 +431,8 @@ __global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__
     bool nom_x, nom_y, lo_x, lo_y;
     classify<R>(cx, wl, nom_x, lo_x);
     classify<R>(cy, hl, nom_y, lo_y);
-    const int ax = dead ? 0 : __float2int_rd(cx) - R - (lo_x ? 1 : 0);
-    const int ay = dead ? 0 : __float2int_rd(cy) - R - (lo_y ? 1 : 0);
+    const int ax = dead ? 0 : __float2int_rd(cx) - R - ((!nom_x && lo_x) ? 1 : 0);
+    const int ay = dead ? 0 : __float2int_rd(cy) - R - ((!nom_y && lo_y) ? 1 : 0);
     const int sh = vec ? (ax & 3) : 0;
     const bool fast = __all_sync(0xffffffffu, dead || (nom_x && nom_y));
     {
@@ -393,7 +464,7 @@ __global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__
     const float* sq = win + win_base<R>(lane);
     // 32-bit element offsets from a per-lane base (L * K * HW < 2^30 is checked on the host)
     float* const ob = P.out + ((size_t)b * P.L * K + (size_t)l * K) * HW + p;
-    const float* rp0 = sq + (lo_y ? PC : 0) + sh + (lo_x ? 1 : 0);
+    const float* rp0 = sq + sh;
 #pragma unroll 1
     for (int jc = 0; jc < SIDE; jc += CH) {
         int yo[CH];
@@ -406,7 +477,7 @@ __global__ void __launch_bounds__(32) lookup_warp_kernel(const __grid_constant__
             yo[k] = min(max(j0 - ay, 0), PR - 2) * PC;
         }
         if (fast) {
-            // nominal taps: with o = (lo ? 1 : 0), x tap i reads stored columns sh+o+i, +1; output row j reads rows o+j, +1
+            // nominal taps: x tap i reads stored columns sh+i, +1; output row j reads window rows j, +1
             float r[CH + 1][SIDE + 1];
             const float* rp = rp0 + jc * PC;
 #pragma unroll
@@ -516,6 +587,12 @@ int launch_taps_r(const LookupParams& P, cudaStream_t s) {
     CF_CHECK_LAUNCH("lookup_taps_kernel");
     return CF_OK;
 }
+
+}  // namespace
+#ifdef CF_BRINGUP
+void lookup_set_timestamps(unsigned long long* p) { cudaMemcpyToSymbol(g_lookup_ts, &p, sizeof(p)); }
+#endif
+namespace {
 
 LookupParams make_params(const float* pyramid, const LevelDims& d, const float* coords, int B, int H, int W, int L) {
     LookupParams P{};

@@ -26,12 +26,14 @@ def _intact(buf, sent=SENT):
     return bool((buf[:PAD] == sent).all()) and bool((buf[-PAD:] == sent).all())
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16", "bf16x3"])
+@pytest.mark.parametrize("precision", ["fp32", "auto", "bf16", "bf16x3"])
 @pytest.mark.parametrize("hw,c,b", [((32, 32), 64, 2), ((28, 28), 40, 1), ((64, 64), 32, 1), ((20, 8), 24, 2), ((17, 21), 16, 1)])
 def test_pyramid_build_stays_inside_its_buffer(precision, hw, c, b):
     cf = _cf()
     from cardioflow_b200 import _cabi
     h, w = hw
+    if precision in ("bf16", "bf16x3") and (h % 4 or w % 8 or c % 8):
+        pytest.skip("an explicit tensor-core precision is an error on shapes off the tcgen05 tiling (test_gpu_corr covers the error)")
     L = 4 if min(h, w) >= 16 else 2
     n = _cabi.lib().cf_corr_pyramid_bytes(b, h, w, L) // 4
     buf, view = _guarded(n)

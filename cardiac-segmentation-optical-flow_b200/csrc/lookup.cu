@@ -64,8 +64,10 @@ struct Geo {
     static constexpr int QP = PR * PC + (((PR * PC / 4) % 2 == 0) ? 4 : 0);   // words per query: QP / 4 odd
     static_assert(QP % 4 == 0 && (QP / 4) % 2 == 1, "window pitch / 4 must be odd");
     static constexpr int WIN = kQT * QP + 16;            // + the 16 B skews of win_base()
-    static constexpr int XT = SIDE * 3 * kQT;            // shared x taps: [SIDE][query] (w_lo, w_hi) pairs, then [SIDE][query] window columns
-    static constexpr size_t SMEM = (size_t)(WIN + XT) * sizeof(float);
+    // 23.1 KB per CTA for r = 4: nine CTAs per SM.  (The x taps used to be computed once per CTA and shared through another
+    // 3.4 KB of shared memory: 8 CTAs per SM, 3.14 waves of CTAs at cfg2 = a fourth, nearly empty round.  Every warp now
+    // computes the x taps of its queries itself: ~130 more ALU instructions per warp, no shared-memory round trip.)
+    static constexpr size_t SMEM = (size_t)WIN * sizeof(float);
 };
 
 struct LookupParams {
@@ -199,14 +201,12 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
 }
 
 template <int R, int NW>
-__global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__ LookupParams P) {
+__global__ void __launch_bounds__(32 * NW, NW == 3 ? 9 : 1) lookup_kernel(const __grid_constant__ LookupParams P) {
     using G = Geo<R>;
     constexpr int SIDE = G::SIDE, PR = G::PR, PC = G::PC;
     constexpr int JPW = (SIDE + NW - 1) / NW;   // output rows (and taps per axis) per warp
     extern __shared__ __align__(16) float smem[];
     float* const win = smem;                    // windows: win_base(q) + row * PC + column
-    float2* const xw = reinterpret_cast<float2*>(smem + G::WIN);   // [SIDE][kQT]: x tap weights (w_lo, w_hi)
-    int* const xc = reinterpret_cast<int*>(smem + G::WIN + 2 * SIDE * kQT);   // [SIDE][kQT]: x tap window column
 
     // Programmatic dependent launch: let the NEXT kernel of the stream (normally the next lookup) be scheduled while this
     // grid drains -- its CTAs become resident and run their index arithmetic, then block in griddepcontrol.wait below
@@ -264,22 +264,24 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     }
 
     CF_TS(2, 0.0f);
-    // taps: warp w computes taps w*JPW.. of both axes; x taps are shared, y taps stay in registers
-    int yoff[JPW];
-    float ywl[JPW], ywh[JPW];
+    // taps (registers): every warp computes the x taps of its 32 queries and the y taps of its own output rows w*JPW..
+    int yoff[JPW], xo[SIDE];
+    float ywl[JPW], ywh[JPW], xwl[SIDE], xwh[SIDE];
     {
         const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
         const float rx = P.rcp_w[l], ry = P.rcp_h[l];
+#pragma unroll
+        for (int i = 0; i < SIDE; ++i) {
+            int i0;
+            axis_tap(cx, i - R, s1x, rx, i0, xwl[i], xwh[i]);
+            xo[i] = min(max(i0 - ax, 0), PR - 2) + sh;
+        }
 #pragma unroll
         for (int k = 0; k < JPW; ++k) {
             const int t = w * JPW + k;
             yoff[k] = 0; ywl[k] = 0.0f; ywh[k] = 0.0f;
             if (t < SIDE) {
                 int i0;
-                float lo, hi;
-                axis_tap(cx, t - R, s1x, rx, i0, lo, hi);
-                xc[t * kQT + lane] = min(max(i0 - ax, 0), PR - 2) + sh;
-                xw[t * kQT + lane] = make_float2(lo, hi);
                 axis_tap(cy, t - R, s1y, ry, i0, ywl[k], ywh[k]);
                 yoff[k] = min(max(i0 - ay, 0), PR - 2) * PC;
             }
@@ -346,7 +348,7 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
         }
 #pragma unroll
         for (int i = 0; i < SIDE; ++i) {
-            const float2 x = xw[i * kQT + lane];                  // (w_lo, w_hi) of x tap i
+            const float2 x = make_float2(xwl[i], xwh[i]);         // (w_lo, w_hi) of x tap i
             const float2 xll = make_float2(x.x, x.x), xhh = make_float2(x.y, x.y);
 #pragma unroll
             for (int kp = 0; kp < NP; ++kp) {
@@ -377,13 +379,11 @@ __global__ void __launch_bounds__(32 * NW) lookup_kernel(const __grid_constant__
     } else {
 #pragma unroll
         for (int i = 0; i < SIDE; ++i) {
-            const int xo = xc[i * kQT + lane];
-            const float2 x = xw[i * kQT + lane];
-            const float xl = x.x, xh = x.y;
+            const float xl = xwl[i], xh = xwh[i];
 #pragma unroll
             for (int k = 0; k < JPW; ++k) {
                 if (j0 + k < SIDE) {
-                    const float* t = sq + yoff[k] + xo;
+                    const float* t = sq + yoff[k] + xo[i];
                     float acc = __fmul_rn(t[0], __fmul_rn(xl, ywl[k]));
                     acc = fmaf(t[1], __fmul_rn(xh, ywl[k]), acc);
                     acc = fmaf(t[PC], __fmul_rn(xl, ywh[k]), acc);

@@ -4,8 +4,9 @@
 //
 //   cf_corr_lookup_bwd   d(lookup)/d(pyramid): every (query, level) owns a private h_l x w_l image, so the 81
 //                        bilinear taps of a query scatter into a window that NO other thread touches -> the
-//                        window is accumulated in shared memory and ADDED to the gradient pyramid with plain
-//                        read-modify-writes (no atomics): the lookups of one CorrBlock share one gradient buffer.
+//                        window is accumulated in shared memory and ADDED to the gradient pyramid with one reduction
+//                        per touched cell (deterministic: one addition per cell and launch): the lookups of one
+//                        CorrBlock share one gradient buffer.
 //                        No gradient w.r.t. coords: the reference detaches them (SegFlowGaussian.py:933).
 //   cf_corr_pool_bwd     backward of the avg_pool2d chain, coarse -> fine, in place: g_l += up2(g_{l+1}) / 4.
 //   cf_corr_volume_bwd   d(corr)/d(fmaps): gf1 = f2 . G^T / sqrt(C), gf2 = f1 . G / sqrt(C) with G = grad of
@@ -104,9 +105,12 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
         for (int c = lane; c < CELLS; c += 32) {
             const int wy = c / PR, wx = c - wy * PR;
             const int y = qy + wy, x = qx + wx;
-            // accumulate: the 12 lookups of one CorrBlock add into ONE gradient pyramid (launches are stream-ordered and a
-            // (query, level) image belongs to one warp, so a plain read-modify-write is race-free)
-            if ((unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl) img[(size_t)y * wl + x] += src[c];
+            // accumulate: the 12 lookups of one CorrBlock add into ONE gradient pyramid.  Launches are stream-ordered and a
+            // (query, level) image belongs to one warp, so every cell receives exactly one addition per launch: a reduction
+            // (RED.ADD.F32, no return value) gives the same bits as load-add-store without the 160 dependent global round
+            // trips per warp that bounded this kernel (220 us per cfg2 lookup at 5 % of HBM).  Cells no tap touched are skipped.
+            const float v = src[c];
+            if (v != 0.0f && (unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl) atomicAdd(&img[(size_t)y * wl + x], v);
         }
     }
 }
@@ -123,6 +127,26 @@ __global__ void __launch_bounds__(256) pool_bwd_kernel(float* __restrict__ fine,
     const long n = r / h;
     const int y2 = y >> 1, x2 = x >> 1;
     if (y2 < h2 && x2 < w2) fine[t] = __fadd_rn(fine[t], __fdiv_rn(__ldg(coarse + ((size_t)n * h2 + y2) * w2 + x2), 4.0f));
+}
+
+// the same for level widths that are multiples of 4: one thread = 4 consecutive cells of a fine row (16-byte accesses, two coarse
+// cells), 32-bit index arithmetic (the scalar kernel spends most of its instructions on three 64-bit divisions)
+__global__ void __launch_bounds__(256) pool_bwd_vec4_kernel(float4* __restrict__ fine, const float2* __restrict__ coarse, int h,
+                                                            int w4, unsigned total4) {
+    const unsigned t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= total4) return;
+    const unsigned x4 = t % (unsigned)w4, r = t / (unsigned)w4;
+    const unsigned y = r % (unsigned)h, n = r / (unsigned)h;
+    const unsigned h2 = (unsigned)h >> 1, y2 = y >> 1;
+    if (y2 >= h2) return;                        // odd last row: outside every pooling window (floor mode)
+    const float2 c = __ldg(coarse + ((size_t)n * h2 + y2) * (unsigned)w4 + x4);
+    const float a = __fdiv_rn(c.x, 4.0f), b = __fdiv_rn(c.y, 4.0f);
+    float4 f = fine[t];
+    f.x = __fadd_rn(f.x, a);
+    f.y = __fadd_rn(f.y, a);
+    f.z = __fadd_rn(f.z, b);
+    f.w = __fadd_rn(f.w, b);
+    fine[t] = f;
 }
 
 // C[m, n] = alpha * sum_k A[m, k] * B(k, n);  A row-major [M, K] (k contiguous).
@@ -232,7 +256,13 @@ int launch_pool_chain_bwd(float* gpyr, const LevelDims& d, long n_img, int L, cu
         float* fine = reinterpret_cast<float*>(base + d.off[l]);
         const float* coarse = reinterpret_cast<const float*>(base + d.off[l + 1]);
         const long total = n_img * d.h[l] * d.w[l];
-        pool_bwd_kernel<<<cdiv(total, 256), 256, 0, s>>>(fine, coarse, d.h[l], d.w[l], total);
+        if (d.w[l] % 4 == 0 && total / 4 < 0xffffffffL && aligned16(fine) && (reinterpret_cast<uintptr_t>(coarse) & 7u) == 0) {
+            const unsigned total4 = (unsigned)(total / 4);
+            pool_bwd_vec4_kernel<<<cdiv((long)total4, 256), 256, 0, s>>>(reinterpret_cast<float4*>(fine), reinterpret_cast<const float2*>(coarse),
+                                                                         d.h[l], d.w[l] / 4, total4);
+        } else {
+            pool_bwd_kernel<<<cdiv(total, 256), 256, 0, s>>>(fine, coarse, d.h[l], d.w[l], total);
+        }
         CF_CHECK_LAUNCH("pool_bwd_kernel");
     }
     return CF_OK;

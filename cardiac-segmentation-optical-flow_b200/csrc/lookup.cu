@@ -111,10 +111,17 @@ __device__ __forceinline__ uint64_t l2_evict_last_policy(float frac = 1.0f) {
     return pol;
 }
 // asynchronous global -> shared copies (LDGSTS): no staging registers, every copy of a warp is in flight at once;
-// src_bytes == 0 writes zeros (zero padding outside the image)
-__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint32_t src_bytes, uint64_t pol) {
-    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2, %3;"
-                 ::"r"(dst), "l"(src), "r"(src_bytes), "l"(pol) : "memory");
+// copies outside the image write zeros (zero padding) and read nothing
+// 16-byte copy, zero-filled outside the image: the copy's own `ignore-src` predicate is formed inside the asm from the two unsigned
+// bounds checks (row >= rows || col >= cols): 2 instructions per copy instead of the 5 the compiler needs to turn a bool into a byte count
+__device__ __forceinline__ void cp_async_16_bounds(uint32_t dst, const void* src, unsigned row, unsigned rows, unsigned col, unsigned cols,
+                                                   uint64_t pol) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ge.u32 p, %2, %3;\n\t"
+        "setp.ge.or.u32 p, %4, %5, p;\n\t"
+        "cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, p, %6;\n\t}"
+        ::"r"(dst), "l"(src), "r"(row), "r"(rows), "r"(col), "r"(cols), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void cp_async_4(uint32_t dst, const void* src, uint32_t src_bytes, uint64_t pol) {
     asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2, %3;"
@@ -169,7 +176,6 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
         const int gx = (VEC ? (q_ax & ~3) : q_ax) + 4 * ch;          // first image column of the chunk
         const bool ch_need = !(q_in & 1u) && ((q_in >> (1 + ch)) & 1u);
         const int skip = (int)((q_in >> 5) & 15u);
-        const bool col_in = (unsigned)gx < (unsigned)wl;              // VEC: chunks are entirely in or out
         const char* gq = TILED ? reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)gx * 4))
                                : reinterpret_cast<const char*>(img0 + ((long)src * img_words + (long)(q_ay + w) * wl + gx));
         const unsigned row_bytes = (unsigned)(NW * wl) * 4u;
@@ -184,10 +190,9 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
                 const char* gp = TILED ? gq + ((yrow >> 2) * tile_row_bytes + (yrow & 3) * 16) : gq + (unsigned)k * row_bytes;
                 const uint32_t d = sq + (uint32_t)(NW * k * PC) * 4u;
                 if (VEC) {
-                    const bool in = row_in && col_in;
-                    // src-size 0: 16 zero bytes are written and nothing is read.  (A/B-tested under ncu: redirecting these requests to one
-                    // valid address changes neither the L2 sector counts nor the time -- profiles/r1_zfill_ab.log.)
-                    cp_async_16(d, gp, in ? 16u : 0u, pol);
+                    // outside the image: 16 zero bytes are written and nothing is read.  (A/B-tested under ncu: redirecting these requests
+                    // to one valid address changes neither the L2 sector counts nor the time -- profiles/r1_zfill_ab.log.)
+                    cp_async_16_bounds(d, gp, (unsigned)yrow, (unsigned)hl, (unsigned)gx, (unsigned)wl, pol);
                 } else {
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {

@@ -205,7 +205,7 @@ __device__ __forceinline__ void stage_windows(uint32_t win_s, const float* __res
     }
 }
 
-template <int R, int NW>
+template <int R, int NW, bool BARREL>
 __global__ void __launch_bounds__(32 * NW, NW == 3 ? 9 : 1) lookup_kernel(const __grid_constant__ LookupParams P) {
     using G = Geo<R>;
     constexpr int SIDE = G::SIDE, PR = G::PR, PC = G::PC;
@@ -322,60 +322,79 @@ __global__ void __launch_bounds__(32 * NW, NW == 3 ? 9 : 1) lookup_kernel(const 
         // nominal taps: x tap i reads stored columns sh+i, +1; output row j reads window rows j, +1.
         // The kernel issues on 63 % of the cycles (ncu), a fifth of them these blends: two output rows are blended at once with the
         // packed fp32 instructions of sm_100 (FMUL2 / FFMA2: IEEE round-to-nearest per component, so every output keeps the exact
-        // sequence fmul, fma, fma, fma in ATen's nw, ne, sw, se order).  Pair kp = rows (2kp, 2kp+1): top[c] = (r[2kp][c], r[2kp+1][c]),
-        // bot[c] = (r[2kp+1][c], r[2kp+2][c]); an odd last row runs the scalar sequence with packed weight products.
-        constexpr int NP = JPW / 2;
+        // sequence fmul, fma, fma, fma in ATen's nw, ne, sw, se order).  Pair kp = output rows (2kp, 2kp+1) from window rows 2kp .. 2kp+2;
+        // an odd last row runs the scalar sequence with packed weight products.
+        // Window rows come into registers one row at a time.  BARREL: four aligned LDS.128 per row (a quarter-warp's eight 16-byte
+        // reads never collide with the window pitch used here) and the lane's alignment shift sh = 0..3 applied in registers by two
+        // select stages (by 2, by 1); otherwise SIDE+1 scalar reads at column sh + c, which collide 2.6-fold when the shifts of the
+        // 32 lanes are unrelated (noise coordinates) and not at all when consecutive queries have consecutive anchors (smooth flows).
+        // Measured at cfg2 with noise coordinates: BARREL cuts the shared-memory wavefronts of a launch from 2.16 M to 1.63 M (conflicts 1.03 M
+        // -> 0.38 M) and is SLOWER (17.2 vs 16.5 us): the launch is bound by the dependent phases of its resident CTAs, not by the LSU.
+        // It stays behind CF_LOOKUP_BARREL=1.
+        constexpr int NP = JPW / 2, NC = SIDE + 1;
         constexpr bool ODD = (JPW & 1) != 0;
-        const float* rp = sq + j0 * PC + sh;
-        float2 top[NP > 0 ? NP : 1][SIDE + 1], bot[NP > 0 ? NP : 1][SIDE + 1], yl2[NP > 0 ? NP : 1], yh2[NP > 0 ? NP : 1];
-        float s0[SIDE + 1], s1[SIDE + 1];            // odd last row: its two window rows
+        const float* const rows = sq + j0 * PC;
+        const bool sh1 = (sh & 1) != 0, sh2 = (sh & 2) != 0;
+        auto load_row = [&](int k, float* v) {           // v[c] = window row j0 + k, column sh + c
+            if (j0 + k > SIDE) {
+#pragma unroll
+                for (int c = 0; c < NC; ++c) v[c] = 0.0f;
+                return;
+            }
+            if (BARREL) {
+                constexpr int NCH = (NC + 3 + 3) / 4;    // chunks covering columns 0 .. NC + 2
+                float wv[NCH * 4], t[NC + 1];
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch) {
+                    const float4 q4 = *reinterpret_cast<const float4*>(rows + k * PC + 4 * ch);
+                    wv[4 * ch] = q4.x; wv[4 * ch + 1] = q4.y; wv[4 * ch + 2] = q4.z; wv[4 * ch + 3] = q4.w;
+                }
+#pragma unroll
+                for (int c = 0; c <= NC; ++c) t[c] = sh2 ? wv[c + 2] : wv[c];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) v[c] = sh1 ? t[c + 1] : t[c];
+            } else {
+#pragma unroll
+                for (int c = 0; c < NC; ++c) v[c] = rows[k * PC + sh + c];
+            }
+        };
+        float ra[NC], rb[NC], rc[NC];
+        load_row(0, ra);
 #pragma unroll
         for (int kp = 0; kp < NP; ++kp) {
             const int k = 2 * kp;
-            yl2[kp] = make_float2(ywl[k], ywl[k + 1]);
-            yh2[kp] = make_float2(ywh[k], ywh[k + 1]);
+            load_row(k + 1, rb);
+            load_row(k + 2, rc);
+            const float2 yl2 = make_float2(ywl[k], ywl[k + 1]), yh2 = make_float2(ywh[k], ywh[k + 1]);
+            if (j0 + k < SIDE) {
 #pragma unroll
-            for (int c = 0; c <= SIDE; ++c) {
-                const float r0 = (j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f;
-                const float r1 = (j0 + k + 1 <= SIDE) ? rp[(k + 1) * PC + c] : 0.0f;
-                const float r2 = (j0 + k + 2 <= SIDE) ? rp[(k + 2) * PC + c] : 0.0f;
-                top[kp][c] = make_float2(r0, r1);
-                bot[kp][c] = make_float2(r1, r2);
-            }
-        }
-        if (ODD) {
-            constexpr int k = JPW - 1;
-#pragma unroll
-            for (int c = 0; c <= SIDE; ++c) {
-                s0[c] = NP > 0 ? bot[NP > 0 ? NP - 1 : 0][c].y : ((j0 + k <= SIDE) ? rp[k * PC + c] : 0.0f);
-                s1[c] = (j0 + k + 1 <= SIDE) ? rp[(k + 1) * PC + c] : 0.0f;
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < SIDE; ++i) {
-            const float2 x = make_float2(xwl[i], xwh[i]);         // (w_lo, w_hi) of x tap i
-            const float2 xll = make_float2(x.x, x.x), xhh = make_float2(x.y, x.y);
-#pragma unroll
-            for (int kp = 0; kp < NP; ++kp) {
-                const int k = 2 * kp;
-                if (j0 + k < SIDE) {
-                    float2 acc = __fmul2_rn(top[kp][i], __fmul2_rn(xll, yl2[kp]));
-                    acc = __ffma2_rn(top[kp][i + 1], __fmul2_rn(xhh, yl2[kp]), acc);
-                    acc = __ffma2_rn(bot[kp][i], __fmul2_rn(xll, yh2[kp]), acc);
-                    acc = __ffma2_rn(bot[kp][i + 1], __fmul2_rn(xhh, yh2[kp]), acc);
+                for (int i = 0; i < SIDE; ++i) {
+                    const float2 xll = make_float2(xwl[i], xwl[i]), xhh = make_float2(xwh[i], xwh[i]);
+                    float2 acc = __fmul2_rn(make_float2(ra[i], rb[i]), __fmul2_rn(xll, yl2));
+                    acc = __ffma2_rn(make_float2(ra[i + 1], rb[i + 1]), __fmul2_rn(xhh, yl2), acc);
+                    acc = __ffma2_rn(make_float2(rb[i], rc[i]), __fmul2_rn(xll, yh2), acc);
+                    acc = __ffma2_rn(make_float2(rb[i + 1], rc[i + 1]), __fmul2_rn(xhh, yh2), acc);
                     __stcs(reinterpret_cast<float*>(ok[k]), acc.x);
                     ok[k] += ostep;
                     if (j0 + k + 1 < SIDE) { __stcs(reinterpret_cast<float*>(ok[k + 1]), acc.y); ok[k + 1] += ostep; }
                 }
             }
-            if (ODD) {
-                constexpr int k = JPW - 1;
-                if (j0 + k < SIDE) {
-                    const float2 wl2 = __fmul2_rn(x, make_float2(ywl[k], ywl[k])), wh2 = __fmul2_rn(x, make_float2(ywh[k], ywh[k]));
-                    float acc = __fmul_rn(s0[i], wl2.x);
-                    acc = fmaf(s0[i + 1], wl2.y, acc);
-                    acc = fmaf(s1[i], wh2.x, acc);
-                    acc = fmaf(s1[i + 1], wh2.y, acc);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) ra[c] = rc[c];
+        }
+        if (ODD) {
+            constexpr int k = JPW - 1;
+            load_row(k + 1, rb);
+            if (j0 + k < SIDE) {
+                const float2 yl1 = make_float2(ywl[k], ywl[k]), yh1 = make_float2(ywh[k], ywh[k]);
+#pragma unroll
+                for (int i = 0; i < SIDE; ++i) {
+                    const float2 x = make_float2(xwl[i], xwh[i]);         // (w_lo, w_hi) of x tap i
+                    const float2 wl2 = __fmul2_rn(x, yl1), wh2 = __fmul2_rn(x, yh1);
+                    float acc = __fmul_rn(ra[i], wl2.x);
+                    acc = fmaf(ra[i + 1], wl2.y, acc);
+                    acc = fmaf(rb[i], wh2.x, acc);
+                    acc = fmaf(rb[i + 1], wh2.y, acc);
                     __stcs(reinterpret_cast<float*>(ok[k]), acc);
                     ok[k] += ostep;
                 }
@@ -563,7 +582,9 @@ int launch_lookup_rw(const LookupParams& P, long ngroups, cudaStream_t s) {
     attr.val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    CF_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lookup_kernel<R, NW>, P));
+    static const bool barrel = [] { const char* e = getenv("CF_LOOKUP_BARREL"); return e ? atoi(e) != 0 : false; }();   // A/B knob: measured slower, see the fast path
+    if (barrel) CF_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lookup_kernel<R, NW, true>, P));
+    else CF_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lookup_kernel<R, NW, false>, P));
     return CF_OK;
 }
 

@@ -167,9 +167,6 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-__device__ __forceinline__ float scale_val(float v, const GemmParams& P) {
-    return P.mul != 0.0f ? __fmul_rn(v, P.mul) : __fdiv_rn(v, P.div);
-}
 __device__ __forceinline__ float pool4(float a, float b, float c, float d) {
     return __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(a, b), c), d), 0.25f);  // /4 is exact as *0.25
 }
@@ -415,8 +412,13 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 float v[32];
                 tmem_ld32(tacc + (uint32_t)(c * 32), v);
                 tmem_wait_ld();
+                if (P.mul != 0.0f) {          // the test stays outside the unrolled loops (inside, it is re-evaluated per element)
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = scale_val(v[i], P);
+                    for (int i = 0; i < 32; ++i) v[i] = __fmul_rn(v[i], P.mul);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = __fdiv_rn(v[i], P.div);
+                }
                 if (ep_tid == 0) tma_store_wait_read<NEPI - 1>();   // the store that used buffer `sb` NEPI chunks ago is done
                 epi_bar_sync();
                 const uint32_t dst = S.epi(sb) + (uint32_t)row * 128u;
@@ -445,8 +447,13 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         tmem_ld8(tacc + (uint32_t)((2 * j) * W + 8 * m), top);
                         tmem_ld8(tacc + (uint32_t)((2 * j + 1) * W + 8 * m), bot);
                         tmem_wait_ld();
+                        if (P.mul != 0.0f) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) { top[i] = scale_val(top[i], P); bot[i] = scale_val(bot[i], P); }
+                            for (int i = 0; i < 8; ++i) { top[i] = __fmul_rn(top[i], P.mul); bot[i] = __fmul_rn(bot[i], P.mul); }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) { top[i] = __fdiv_rn(top[i], P.div); bot[i] = __fdiv_rn(bot[i], P.div); }
+                        }
                         float4 o;
                         o.x = pool4(top[0], top[1], bot[0], bot[1]);
                         o.y = pool4(top[2], top[3], bot[2], bot[3]);

@@ -54,6 +54,7 @@ _SIGNATURES = {
     "cf_corr_pool_bwd": (_I, [_P, _I, _I, _I, _I, _P]),
     "cf_corr_volume_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_corr_volume_bwd_workspace_bytes": (_Z, [_I, _I, _I, _I]),
+    "cf_corr_volume_bwd_noalloc": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_corr_volume_bwd_ex": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _Z, _c.POINTER(_I), _P]),
     "cf_vecint": (_I, [_P, _I, _I, _I, _I, _P, _P, _P]),
     "cf_sample_points": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P]),

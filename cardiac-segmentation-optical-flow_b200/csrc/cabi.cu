@@ -371,6 +371,14 @@ int cf_corr_volume_bwd_ex(const float* f1, const float* f2, const float* grad_co
     return launch_corr_volume_bwd(f1, f2, grad_corr, B, C, H * W, grad_f1, grad_f2, (cudaStream_t)stream);
 }
 
+int cf_corr_volume_bwd_noalloc(const float* f1, const float* f2, const float* grad_corr, int B, int C, int H, int W,
+                               float* grad_f1, float* grad_f2, void* stream) {
+    CF_REQUIRE(f1 && f2 && grad_corr, CF_ERR_BAD_ARG, "cf_corr_volume_bwd_noalloc: null pointer");
+    CF_REQUIRE(grad_f1 || grad_f2, CF_ERR_BAD_ARG, "cf_corr_volume_bwd_noalloc: neither grad_f1 nor grad_f2 requested");
+    CF_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, CF_ERR_BAD_ARG, "cf_corr_volume_bwd_noalloc: bad shape");
+    return launch_corr_volume_bwd_tc_noalloc(f1, f2, grad_corr, B, C, H * W, grad_f1, grad_f2, (cudaStream_t)stream);
+}
+
 int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream) {
     CF_REQUIRE(vec && out, CF_ERR_BAD_ARG, "cf_vecint: null pointer");
     CF_REQUIRE(B > 0 && H > 1 && W > 1, CF_ERR_BAD_ARG, "cf_vecint: bad shape B=%d H=%d W=%d", B, H, W);

@@ -125,6 +125,9 @@ bool corr_bwd_tc_supported(int B, int C, int HW);
 size_t corr_bwd_tc_workspace_bytes(int B, int C, int HW);
 int launch_corr_volume_bwd_tc(const float* f1, const float* f2, const float* gcorr, int B, int C, int HW, float* gf1,
                               float* gf2, void* ws, size_t ws_bytes, cudaStream_t s);
+// the same with the planes in a static device array (corr_bwd_tc_noalloc.inl): no allocation, sizes up to CF_NOALLOC_SCRATCH_BYTES
+int launch_corr_volume_bwd_tc_noalloc(const float* f1, const float* f2, const float* gcorr, int B, int C, int HW, float* gf1,
+                                      float* gf2, cudaStream_t s);
 
 int launch_lookup(const float* pyramid, const LevelDims& d, const float* coords, int B, int H, int W, int L,
                   int r, float* out, unsigned tiled_mask /* bit l: level l stored as 4x4 tiles */, cudaStream_t s);

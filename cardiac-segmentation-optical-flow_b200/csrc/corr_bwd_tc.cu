@@ -162,3 +162,4 @@ __global__ void __launch_bounds__(256) split_planes_kernel(const float* __restri
 }  // namespace cf
 
 #include "corr_bwd_tc_host.inl"
+#include "corr_bwd_tc_noalloc.inl"

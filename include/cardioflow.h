@@ -198,6 +198,18 @@ CF_API int cf_corr_volume_bwd_ex(const float* f1, const float* f2, const float* 
                           int precision, float* grad_f1 /* may be NULL */, float* grad_f2 /* may be NULL */, void* workspace,
                           size_t workspace_bytes, int* used_precision /* may be NULL */, void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate device memory
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  cf_corr_volume_bwd_ex's tensor-core
+ * path with its scratch (the four bf16 hi / lo planes of the feature maps) in a static device array of CF_NOALLOC_SCRATCH_BYTES
+ * that every GPU loading the library holds until exit: the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine).  Same results as cf_corr_volume_bwd_ex(..., CF_PREC_BF16X3, ...).  Errors (CF_ERR_UNSUPPORTED, nothing is
+ * launched): H*W % 8 != 0, or 4 * round_up_256(B*C*H*W*2) > CF_NOALLOC_SCRATCH_BYTES (e.g. up to B = 4 at C = 256, 32 x 32).
+ * All calls on a device share the array, which keeps the previous call's contents (nothing in it needs clearing: each call
+ * overwrites what it reads); calls that overlap on the GPU -- different streams, concurrently replayed graphs -- RACE on it. */
+#define CF_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
+CF_API int cf_corr_volume_bwd_noalloc(const float* f1, const float* f2, const float* grad_corr /* level 0 */, int B, int C, int H,
+                               int W, float* grad_f1 /* may be NULL */, float* grad_f2 /* may be NULL */, void* stream);
+
 /* VecInt (integration.py:82-99): vec/2^n then n x (vec += warp(vec, vec)); work = scratch [B,2,H,W]. */
 CF_API int cf_vecint(const float* vec, int B, int H, int W, int nsteps, float* out, float* work, void* stream);
 

@@ -29,7 +29,7 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:look
 timeout 300 python tools/kbench.py cfg4 --only lookup --reps 6 > $O/plain_l4.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:lookup_kernel -s 30 -c 1 -o $O/r2_ncu_lookup_cfg4 python tools/kbench.py cfg4 --only lookup --reps 6 > $O/ncu_l4.log 2>&1
 timeout 300 python tools/kbench.py cfg3 --only warp --reps 6 > $O/plain_w.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:warp2d_tile -s 60 -c 2 -o $O/r2_ncu_warp python tools/kbench.py cfg3 --only warp --reps 6 > $O/ncu_w.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:warp2d_tile -s 6 -c 2 -o $O/r2_ncu_warp python tools/kbench.py cfg3 --only warp --reps 6 > $O/ncu_w.log 2>&1
 KB_SKIP_SIMT_BWD=1 timeout 300 python tools/kbench.py cfg2 --only bwd --reps 6 > $O/plain_bw.log 2>&1 &&
 KB_SKIP_SIMT_BWD=1 timeout 900 ncu --set full --clock-control none --import-source on -k regex:corr_bwd_tc -s 2 -c 1 -o $O/r2_ncu_corr_bwd_tc python tools/kbench.py cfg2 --only bwd --reps 6 > $O/ncu_bw.log 2>&1
 for r in lookup corr_tc2 lookup_tc lookup_cfg4 warp corr_bwd_tc; do python tools/ncu_brief.py $O/r2_ncu_$r.ncu-rep > $O/r2_ncu_$r.txt 2>&1; done

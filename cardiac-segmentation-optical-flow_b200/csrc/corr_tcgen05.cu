@@ -231,6 +231,9 @@ corr_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
+            // the operands are written by the pre-pass right before this launch (launched with the PDL attribute: no effect otherwise);
+            // this thread is the only one that reads them, and every store of this grid comes after MMAs that need these loads
+            asm volatile("griddepcontrol.wait;" ::: "memory");
             mbar_expect_tx(bar(kBarAFull), (uint32_t)k_blocks * (BM * 128u));   // out-of-range channels / rows are zero-filled
             for (int kc = 0; kc < k_blocks; ++kc)
                 tma_load_3d(S.a + (uint32_t)kc * (BM * 128u), &tmA, bar(kBarAFull), kc * BK, m0, b);
@@ -533,6 +536,9 @@ __global__ void __launch_bounds__(256) to_bf16_t_kernel(const float* __restrict_
                                                         __nv_bfloat16* __restrict__ oa, __nv_bfloat16* __restrict__ ob, int C,
                                                         int HW) {
     __shared__ float tile[64][65];
+    // programmatic dependent launch: the GEMM that follows in the stream may become resident (barrier set-up, TMEM allocation, tensor-map
+    // prefetch) while this grid drains; its producer thread waits for this grid's completion before its first TMA load
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int which = blockIdx.z & 1, bi = blockIdx.z >> 1;
     const float* src = (which ? b : a) + (size_t)bi * C * HW;
     __nv_bfloat16* dst = (which ? ob : oa) + (size_t)bi * HW * C;
@@ -677,9 +683,19 @@ int launch_corr_tcgen05(const float* f1, const float* f2, int B, int C, int H, i
         if (rc2) return rc2;
     }
     const long grid = (long)B * P.m_tiles * P.n_split;
-    if (w32) corr_tcgen05_kernel<true><<<(unsigned)grid, NTHREADS, smem, s>>>(tmA, tmB, tmC, tmL1, P);
-    else corr_tcgen05_kernel<false><<<(unsigned)grid, NTHREADS, smem, s>>>(tmA, tmB, tmC, tmL1, P);
-    CF_CHECK_LAUNCH("corr_tcgen05_kernel");
+    static const bool pdl = [] { const char* e = getenv("CF_GEMM_PDL"); return e ? atoi(e) != 0 : true; }();   // A/B knob
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    if (w32) CF_CHECK_CUDA(cudaLaunchKernelEx(&cfg, corr_tcgen05_kernel<true>, tmA, tmB, tmC, tmL1, P));
+    else CF_CHECK_CUDA(cudaLaunchKernelEx(&cfg, corr_tcgen05_kernel<false>, tmA, tmB, tmC, tmL1, P));
     return CF_OK;
 }
 

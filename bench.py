@@ -992,6 +992,12 @@ def main():
                      "frac_of_nominal_8000": achieved / 8000.0},
     }
     line["config"]["host_affinity"] = affinity
+    if traffic:
+        # informational: what the launch moves through DRAM (ncu, steady state: profiles/lookup_traffic.json) over the live launch time --
+        # how close the kernel is to the measured HBM peak on the bytes it really moves; `frac` stays on the algorithmic bytes
+        line["roofline"]["dram_traffic_over_launch_time"] = {"gbytes_per_s": traffic / (lookup_ms * 1e-3) / 1e9,
+                                                             "frac_of_peak": traffic / (lookup_ms * 1e-3) / 1e9 / peak,
+                                                             "traffic_over_algorithmic": traffic / lookup_bytes}
     if lane_lookup_ms:
         # informational: the same kernel as the step runs it (one chain per lane, lanes concurrent): bytes of the whole batch over the
         # elapsed time per lookup iteration.  `frac` above stays the conservative single-launch figure.

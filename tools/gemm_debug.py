@@ -1,4 +1,6 @@
 import sys, os
+# needs a bring-up build: CF_NVCC_EXTRA=-DCF_BRINGUP python cardiac-segmentation-optical-flow_b200/_build.py (after touching corr_tcgen05.cu and cabi.cu);
+# the shipped library does not export cf_debug_set_gemm_*
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, ctypes
 import cardioflow_b200 as cf

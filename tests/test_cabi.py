@@ -171,3 +171,33 @@ def test_ncc_host_contract_without_a_gpu():
         == _cabi.CF_ERR_UNSUPPORTED and b"win 7" in lib.cf_last_error()
     assert lib.cf_ncc_workspace_bytes(300, 224, 224, 0) % 256 == 0 and lib.cf_ncc_workspace_bytes(0, 8, 8, 1) == 0
     assert lib.cf_sum_f64(None, 4, None, None, 0, None) == _cabi.CF_ERR_BAD_ARG and lib.cf_sum_f64_workspace_bytes() >= 8
+
+
+def test_round2_entry_points_validate_their_arguments_without_a_gpu():
+    """Null pointers / impossible shapes are rejected by the C ABI itself (CF_ERR_BAD_ARG or CF_ERR_UNSUPPORTED, with a message that
+    names the call) before anything touches CUDA: the checks run here, on a box without a GPU."""
+    import ctypes
+    lib = _cabi.lib()
+    N = None
+    used, tiled = ctypes.c_int(0), ctypes.c_uint(0)
+    one = ctypes.c_void_p(256)          # a non-null pointer that is never dereferenced: every call below fails validation first
+    calls = {
+        "cf_corr_build_ex": lambda: lib.cf_corr_build_ex(N, N, 0, 0, 1, 8, 8, 8, 2, 0, 0, N, N, 0, ctypes.byref(used), ctypes.byref(tiled), N),
+        "cf_corr_build_ex/shape": lambda: lib.cf_corr_build_ex(one, one, 0, 0, 0, 8, 8, 8, 2, 0, 0, one, N, 0, ctypes.byref(used), ctypes.byref(tiled), N),
+        "cf_corr_volume_bwd_ex": lambda: lib.cf_corr_volume_bwd_ex(N, N, N, 1, 8, 8, 8, 0, N, N, N, 0, ctypes.byref(used), N),
+        "cf_corr_volume_bwd_ex/no output": lambda: lib.cf_corr_volume_bwd_ex(one, one, one, 1, 8, 8, 8, 0, N, N, N, 0, ctypes.byref(used), N),
+        "cf_corr_volume_bwd_ex/precision": lambda: lib.cf_corr_volume_bwd_ex(one, one, one, 1, 8, 8, 8, _cabi.PREC_BF16, one, N, N, 0, ctypes.byref(used), N),   # plain bf16 is not a backward precision
+        "cf_corr_volume_bwd_noalloc": lambda: lib.cf_corr_volume_bwd_noalloc(N, N, N, 1, 8, 8, 8, N, N, N),
+        "cf_corr_volume_bwd_noalloc/shape": lambda: lib.cf_corr_volume_bwd_noalloc(one, one, one, 1, 0, 8, 8, one, N, N),
+        "cf_corr_volume_bwd": lambda: lib.cf_corr_volume_bwd(N, N, N, 1, 8, 8, 8, N, N, N),
+    }
+    for name, call in calls.items():
+        rc = call()
+        msg = lib.cf_last_error().decode()
+        assert rc in (_cabi.CF_ERR_BAD_ARG, _cabi.CF_ERR_UNSUPPORTED), (name, rc, msg)
+        assert msg, name
+        if "/" not in name:             # null-pointer checks name the call (cf_corr_build_ex reports as the cf_corr_build family)
+            assert name.replace("_ex", "") in msg, (name, msg)
+    # size queries answer without a GPU as well
+    assert lib.cf_corr_volume_bwd_workspace_bytes(1, 8, 5, 5) == 0          # H*W = 25: no tensor-core path
+    assert lib.cf_corr_volume_bwd_workspace_bytes(0, 8, 8, 8) == 0

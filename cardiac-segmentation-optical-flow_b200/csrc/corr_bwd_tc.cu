@@ -27,7 +27,9 @@ constexpr int BM = 128, BN = 128, BK = 64, UK = 16;
 constexpr int NSTAGE = 3;
 constexpr uint32_t TILE_BYTES = 128u * 128u;             // one operand tile: 128 rows x 64 bf16
 constexpr uint32_t STAGE_BYTES = 4u * TILE_BYTES;        // A hi, A lo, B hi, B lo
-constexpr int LOADER_WARPS = 8, GROUP_WARPS = 4;
+constexpr int LOADER_WARPS = 16, GROUP_WARPS = 8;   // two groups of 8 warps (a thread = 4 chunks of a K block); with 2 x 4 warps there was one
+                                                    // loader warp per scheduler and the kernel ran at its dependent-issue latency (1.7 us per K block)
+constexpr int CPT = 128 * 8 / (32 * GROUP_WARPS);   // 16-byte chunks (8 K values of one operand row) per loader thread and K block
 constexpr int NTHREADS = 64 + 32 * LOADER_WARPS;
 constexpr int TMEM_COLS = BN;
 constexpr size_t kSmemBytes = 1024 + (size_t)NSTAGE * STAGE_BYTES + 256;

@@ -1,10 +1,12 @@
-// Loader / epilogue role of corr_bwd_tc_kernel (included inside the kernel body; warps 2-9).
+// Loader / epilogue role of corr_bwd_tc_kernel (included inside the kernel body; warps 2 .. 2 + LOADER_WARPS - 1).
         // =============================================================================================================
-        // Group g (warps 2 + 4g .. 5 + 4g) owns the K blocks kb = g (mod 2).  128 threads cover one 128 x 64 tile of G:
-        //   gemm 0 (rows = p, K = q): thread -> operand row (tl >> 3) + 16 i, chunk tl & 7: two float4 loads, 8 lanes = 256 contiguous bytes;
-        //   gemm 1 (rows = q, K = p): thread -> operand row tl, chunk i: eight scalar loads down a column of G, lanes along q (coalesced).
-        // Either way the thread ends up with 8 x (8 consecutive K values of one operand row) = eight 16-byte chunks per precision part.
-        const int lw = warp - 2, grp = lw >> 2, tl = (lw & 3) * 32 + lane;
+        // Group g (GROUP_WARPS warps) owns the K blocks kb = g (mod 2).  Its 32 * GROUP_WARPS threads cover one 128 x 64 tile of G:
+        //   gemm 0 (rows = p, K = q): thread -> operand rows (tl >> 3) + 32 i, chunk tl & 7: two float4 loads, 8 lanes = 256 contiguous bytes;
+        //   gemm 1 (rows = q, K = p): thread -> operand row tl & 127, chunks 4 (tl >> 7) + i: eight scalar loads down a column of G per chunk,
+        //   lanes along q (coalesced).
+        // Either way the thread ends up with CPT x (8 consecutive K values of one operand row) = CPT 16-byte chunks per precision part.
+        const int lw = warp - 2, grp = lw / GROUP_WARPS, tl = (lw % GROUP_WARPS) * 32 + lane;      // tl: 0 .. 32 * GROUP_WARPS - 1
+        constexpr int GT = 32 * GROUP_WARPS;             // threads of a group
         const float* const gb = P.g + (size_t)b * HW * HW;
 
         auto issue = [&](int kb, float* v) {
@@ -12,8 +14,8 @@
             if (gemm == 0) {
                 const int chunk = tl & 7, k = k0 + 8 * chunk;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int m = m0 + (tl >> 3) + 16 * i;
+                for (int i = 0; i < CPT; ++i) {
+                    const int m = m0 + (tl >> 3) + (GT / 8) * i;
                     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
                     if (m < HW && k < HW) {                  // HW % 8 == 0: a chunk is inside or outside as a whole
                         const float4* src = reinterpret_cast<const float4*>(gb + (size_t)m * HW + k);
@@ -24,13 +26,13 @@
                     v[8 * i + 4] = c.x; v[8 * i + 5] = c.y; v[8 * i + 6] = c.z; v[8 * i + 7] = c.w;
                 }
             } else {
-                const int m = m0 + tl;
+                const int m = m0 + (tl & 127), cbase = CPT * (tl >> 7);      // operand row, first chunk of this thread
                 const bool row_in = m < HW;
-                const float* src = gb + (size_t)k0 * HW + m;
+                const float* src = gb + (size_t)(k0 + 8 * cbase) * HW + m;
                 const unsigned uHW = (unsigned)HW;               // element offsets inside one pair's G fit 32 bits (HW <= 65535)
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const bool in = row_in && k0 + 8 * i < HW;
+                for (int i = 0; i < CPT; ++i) {
+                    const bool in = row_in && k0 + 8 * (cbase + i) < HW;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[8 * i + j] = in ? __ldg(src + (unsigned)(8 * i + j) * uHW) : 0.0f;
                 }
@@ -41,8 +43,8 @@
             mbar_wait(bar(kEmpty + s), (uint32_t)(((kb / NSTAGE) & 1) ^ 1));
             uint8_t* const ahi = gen + (size_t)s * STAGE_BYTES;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int row = gemm == 0 ? (tl >> 3) + 16 * i : tl, chunk = gemm == 0 ? (tl & 7) : i;
+            for (int i = 0; i < CPT; ++i) {
+                const int row = gemm == 0 ? (tl >> 3) + (GT / 8) * i : (tl & 127), chunk = gemm == 0 ? (tl & 7) : CPT * (tl >> 7) + i;
                 uint4 hi, lo;
                 split8(v + 8 * i, hi, lo);
                 const uint32_t off = (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);   // SWIZZLE_128B, K-major
@@ -55,7 +57,7 @@
         };
 
         {
-            float va[64], vb[64];
+            float va[8 * CPT], vb[8 * CPT];
             int kb = grp;
             if (kb < KB) issue(kb, va);
             while (kb < KB) {
@@ -77,7 +79,8 @@
             const int m = m0 + quad * 32 + lane;
             float* const o = P.out[gemm] + (size_t)b * P.C * HW + m;
 #pragma unroll 1
-            for (int c0 = grp * 64; c0 < grp * 64 + 64; c0 += 32) {
+            constexpr int CW = BN / (LOADER_WARPS / 4);        // columns per warp: the warps of a lane quadrant split the 128 channels
+            for (int c0 = (lw >> 2) * CW; c0 < (lw >> 2) * CW + CW; c0 += 32) {
                 float v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
                 tmem_wait_ld();

@@ -63,34 +63,102 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
     anchor[lane][0] = dead ? (1 << 30) : ax;   // far outside any image: nothing is written back
     anchor[lane][1] = ay;
     float* my = win + lane * PITCH;
+    // taps of both axes up front: they decide between the register path (every tap of every lane is the nominal one: x tap i at
+    // window column i + 1, y tap j at window row j + 1 -- all but queries within ~1e-5 of an integer coordinate) and the general path
+    int xo[SIDE], yo[SIDE];
+    float xl[SIDE], xh[SIDE], yl[SIDE], yh[SIDE];
+    bool nominal = true;
+    {
+        const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
+        const float rcx = __frcp_rn(s1x), rcy = __frcp_rn(s1y);   // IEEE-rounded reciprocals for div_small
+        const float ccx = dead ? 0.0f : cx, ccy = dead ? 0.0f : cy;
+#pragma unroll
+        for (int i = 0; i < SIDE; ++i) {
+            int i0, j0;
+            axis_tap(ccx, i - R, s1x, rcx, i0, xl[i], xh[i]);
+            axis_tap(ccy, i - R, s1y, rcy, j0, yl[i], yh[i]);
+            xo[i] = i0 - ax;   // in [0, PR-2] by the round-trip bound (lookup.cu: classify)
+            yo[i] = j0 - ay;
+            nominal = nominal && xo[i] == i + 1 && yo[i] == i + 1;
+        }
+    }
+    const float* g = P.go + ((size_t)b * P.L * K + (size_t)l * K) * P.HW + p;
+    const bool fastw = __all_sync(0xffffffffu, dead || nominal);
+    if (fastw) {
+        // register path: window row r receives output row j = r - 1 through its upper weights and j = r - 2 through its lower ones; a row
+        // is accumulated in 12 registers with static indices (no shared-memory read-modify-write chain: the general path below spends
+        // 324 dependent LDS / FFMA / STS round trips per query) and stored once.  Rows / columns 0 and PR - 1 stay untouched and unread.
+        float gprev[SIDE], gcur[SIDE];
+#pragma unroll
+        for (int i = 0; i < SIDE; ++i) gprev[i] = gcur[i] = 0.0f;
+#pragma unroll
+        for (int r = 1; r <= SIDE + 1; ++r) {
+            float acc[PR];
+#pragma unroll
+            for (int c = 0; c < PR; ++c) acc[c] = 0.0f;
+            if (r - 1 < SIDE) {
+#pragma unroll
+                for (int i = 0; i < SIDE; ++i) gcur[i] = dead ? 0.0f : __ldg(g + (size_t)(i * SIDE + (r - 1)) * P.HW);   // coalesced across lanes
+#pragma unroll
+                for (int i = 0; i < SIDE; ++i) {
+                    acc[i + 1] = fmaf(gcur[i], xl[i] * yl[r - 1], acc[i + 1]);
+                    acc[i + 2] = fmaf(gcur[i], xh[i] * yl[r - 1], acc[i + 2]);
+                }
+            }
+            if (r - 2 >= 0) {
+#pragma unroll
+                for (int i = 0; i < SIDE; ++i) {
+                    acc[i + 1] = fmaf(gprev[i], xl[i] * yh[r - 2], acc[i + 1]);
+                    acc[i + 2] = fmaf(gprev[i], xh[i] * yh[r - 2], acc[i + 2]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < SIDE; ++i) gprev[i] = gcur[i];
+#pragma unroll
+            for (int c = 1; c <= SIDE + 1; ++c) my[r * PR + c] = acc[c];
+        }
+        __syncwarp();
+        // cooperative write-back of the (2r+2)^2 touched cells: a lane's cells are the same for every query, so their window coordinates
+        // are computed once
+        constexpr int TS = SIDE + 1, TCELLS = TS * TS, NIT = (TCELLS + 31) / 32;
+        int wyk[NIT], wxk[NIT];
+#pragma unroll
+        for (int k = 0; k < NIT; ++k) {
+            const int c = lane + 32 * k;
+            wyk[k] = c < TCELLS ? 1 + c / TS : -1;
+            wxk[k] = 1 + c % TS;
+        }
+        const int nq = (int)min((long)kQ, P.N - n0);
+        for (int q = 0; q < nq; ++q) {
+            const int qx = anchor[q][0], qy = anchor[q][1];
+            if (qx == (1 << 30)) continue;
+            float* img = P.glevel[l] + (size_t)(n0 + q) * hl * wl;
+            const float* srcw = win + q * PITCH;
+#pragma unroll
+            for (int k = 0; k < NIT; ++k) {
+                const int y = qy + wyk[k], x = qx + wxk[k];
+                if (wyk[k] >= 0 && (unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl) {
+                    const float v = srcw[wyk[k] * PR + wxk[k]];
+                    if (v != 0.0f) atomicAdd(&img[y * wl + x], v);      // one addition per cell and launch: deterministic (see below)
+                }
+            }
+        }
+        return;
+    }
     for (int i = 0; i < CELLS; ++i) my[i] = 0.0f;
 
     if (!dead) {
-        int xo[SIDE];
-        float xl[SIDE], xh[SIDE];
-        const float s1x = (float)(wl - 1), s1y = (float)(hl - 1);
-        const float rcx = __frcp_rn(s1x), rcy = __frcp_rn(s1y);   // IEEE-rounded reciprocals for div_small
-#pragma unroll
-        for (int i = 0; i < SIDE; ++i) {
-            int i0;
-            axis_tap(cx, i - R, s1x, rcx, i0, xl[i], xh[i]);
-            xo[i] = i0 - ax;   // in [0, PR-2] by the round-trip bound (lookup.cu: nominal_taps)
-        }
-        const float* g = P.go + ((size_t)b * P.L * K + (size_t)l * K) * P.HW + p;
 #pragma unroll 1
         for (int j = 0; j < SIDE; ++j) {
-            int j0;
-            float yl, yh;
-            axis_tap(cy, j - R, s1y, rcy, j0, yl, yh);
-            float* rowp = my + min(max(j0 - ay, 0), PR - 2) * PR;
+            float* rowp = my + min(max(yo[j], 0), PR - 2) * PR;
 #pragma unroll
             for (int i = 0; i < SIDE; ++i) {
                 const float gv = __ldg(g + (size_t)(i * SIDE + j) * P.HW);   // coalesced across lanes
                 float* c = rowp + min(max(xo[i], 0), PR - 2);
-                c[0] += gv * (xl[i] * yl);
-                c[1] += gv * (xh[i] * yl);
-                c[PR] += gv * (xl[i] * yh);
-                c[PR + 1] += gv * (xh[i] * yh);
+                c[0] += gv * (xl[i] * yl[j]);
+                c[1] += gv * (xh[i] * yl[j]);
+                c[PR] += gv * (xl[i] * yh[j]);
+                c[PR + 1] += gv * (xh[i] * yh[j]);
             }
         }
     }

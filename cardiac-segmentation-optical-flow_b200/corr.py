@@ -180,6 +180,71 @@ class _CorrLookup(torch.autograd.Function):
         return (g if first else None), None, None, None, None, None
 
 
+class _OtfBuild(torch.autograd.Function):
+    """Autograd anchor of an on-the-fly block: (fmap1, fmap2) -> a one-element token that the block's lookups depend on.  No volume
+    exists in the forward pass; the BACKWARD pass materialises the gradient pyramid (the lookups' backward kernels accumulate into
+    one buffer of the volume's size, 4/3 * B * (H*W)^2 floats, allocated when the first of them runs) and then differentiates
+    the correlation exactly as the materialised path does (cf_corr_pool_bwd, cf_corr_volume_bwd_ex)."""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, meta, gstate):
+        ctx.save_for_backward(_cabi.f32c(fmap1), _cabi.f32c(fmap2))
+        ctx.meta = meta
+        ctx.gstate = gstate
+        return torch.zeros(1, dtype=torch.float32, device=fmap1.device)
+
+    @staticmethod
+    def backward(ctx, grad_token):
+        f1, f2 = ctx.saved_tensors
+        B, C, H, W, L = ctx.meta
+        g = ctx.gstate.pop("buf", None)
+        ctx.gstate.pop("task", None)
+        if g is None:                           # no lookup took part in this backward pass
+            return torch.zeros_like(f1), torch.zeros_like(f2), None, None
+        lib = _cabi.lib()
+        gf1, gf2 = torch.empty_like(f1), torch.empty_like(f2)
+        with torch.cuda.device(f1.device):
+            s = _cabi.stream()
+            _cabi.check(lib.cf_corr_pool_bwd(g.data_ptr(), B, H, W, L, s), "cf_corr_pool_bwd")
+            ws_bytes = lib.cf_corr_volume_bwd_workspace_bytes(B, C, H, W)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=f1.device) if ws_bytes else None
+            used = _cabi.ctypes.c_int(0)
+            _cabi.check(lib.cf_corr_volume_bwd_ex(f1.data_ptr(), f2.data_ptr(), g.data_ptr(), B, C, H, W, _cabi.PRECISIONS["auto"],
+                                                  gf1.data_ptr() if ctx.needs_input_grad[0] else None,
+                                                  gf2.data_ptr() if ctx.needs_input_grad[1] else None,
+                                                  ws.data_ptr() if ws is not None else None, ws_bytes,
+                                                  _cabi.ctypes.byref(used), s), "cf_corr_volume_bwd_ex")
+        return (gf1 if ctx.needs_input_grad[0] else None), (gf2 if ctx.needs_input_grad[1] else None), None, None
+
+
+class _OtfLookup(torch.autograd.Function):
+    """On-the-fly lookup inside an autograd graph: forward = the block's volume-free kernel; backward = cf_corr_lookup_bwd into the
+    block's shared gradient pyramid (see _OtfBuild).  No gradient w.r.t. coords (the reference detaches them, SegFlowGaussian.py:933)."""
+
+    @staticmethod
+    def forward(ctx, token, coords, block, out=None):
+        res = block._lookup_on_the_fly(coords, out)
+        ctx.save_for_backward(_cabi.f32c(coords))
+        ctx.meta = block._meta
+        ctx.gstate = block._gstate
+        return res
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (c,) = ctx.saved_tensors
+        B, H, W, L, r = ctx.meta
+        lib = _cabi.lib()
+        task = torch._C._current_graph_task_id()
+        if ctx.gstate.get("buf") is None or ctx.gstate.get("task") != task:
+            numel = lib.cf_corr_pyramid_bytes(B, H, W, L) // 4
+            ctx.gstate["buf"], ctx.gstate["task"] = torch.zeros(numel, dtype=torch.float32, device=grad_out.device), task
+        go = grad_out.contiguous().float()
+        with torch.cuda.device(go.device):
+            _cabi.check(lib.cf_corr_lookup_bwd(c.data_ptr(), go.data_ptr(), B, H, W, L, r, ctx.gstate["buf"].data_ptr(),
+                                               _cabi.stream()), "cf_corr_lookup_bwd")
+        return torch.zeros(1, dtype=torch.float32, device=go.device), None, None, None
+
+
 class CorrBlock:
     """Drop-in for RAFT's ``CorrBlock(fmap1, fmap2, num_levels=4, radius=4)``; instances are callable.
 
@@ -210,12 +275,14 @@ class CorrBlock:
         self._meta = (B, H, W, num_levels, radius)
         self.on_the_fly = bool(on_the_fly)
         if self.on_the_fly:
-            # K4: keep fmap1 and the pooled fmap2 pyramid, recompute window correlations per lookup (fp32;
-            # forward only -- the training graph goes through the materialised path)
-            if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
-                raise NotImplementedError("on_the_fly=True is a forward-only path; use it under torch.no_grad()")
+            # K4: keep fmap1 and the pooled fmap2 pyramid, recompute window correlations per lookup.  Under autograd the forward pass
+            # still holds no volume; the backward pass materialises the gradient pyramid once (see _OtfBuild)
             lib = _cabi.lib()
             C = fmap1.shape[1]
+            self._token = None
+            if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+                self._gstate = {}
+                self._token = _OtfBuild.apply(fmap1, fmap2, (B, C, H, W, num_levels), self._gstate)
             self._f1 = _cabi.f32c(fmap1)
             f2 = _cabi.f32c(fmap2)
             self._f2_pyramid = torch.empty(lib.cf_fmap_pyramid_bytes(B, C, H, W, num_levels) // 4, dtype=torch.float32,
@@ -295,6 +362,8 @@ class CorrBlock:
         if tuple(coords.shape) != (B, 2, H, W):
             raise ValueError(f"coords must be [{B}, 2, {H}, {W}], got {tuple(coords.shape)}")
         if self.on_the_fly:
+            if getattr(self, "_token", None) is not None and torch.is_grad_enabled():
+                return _OtfLookup.apply(self._token, coords, self, out)
             return self._lookup_on_the_fly(coords, out)
         _cabi.require_cuda(self._pyramid, coords)
         return _CorrLookup.apply(self._pyramid, coords, self._meta, out, self._tiled_mask, getattr(self, "_gstate", None))

@@ -19,6 +19,15 @@ namespace {
 
 constexpr int kQ = 32;   // queries per CTA (lane <-> query)
 
+// *p += v unless v == 0 (cells no tap touched, and cells outside the image, which the caller passes as 0), as ONE predicated reduction
+__device__ __forceinline__ void red_add_if_nonzero(float* p, float v) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.neu.f32 q, %1, 0f00000000;\n\t"
+        "@q red.global.add.f32 [%0], %1;\n\t}"
+        ::"l"(p), "f"(v) : "memory");
+}
+
 struct LookupBwdParams {
     float* glevel[CF_MAX_LEVELS];
     int lh[CF_MAX_LEVELS];
@@ -136,11 +145,12 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
             const float* srcw = win + q * PITCH;
 #pragma unroll
             for (int k = 0; k < NIT; ++k) {
+                // branch-free: a predicated shared load and a predicated reduction (as `if`s each cell cost a divergence region of
+                // its own: BSSY / branch / BSYNC -- 5000 instructions per warp in a kernel that runs at its issue latency)
                 const int y = qy + wyk[k], x = qx + wxk[k];
-                if (wyk[k] >= 0 && (unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl) {
-                    const float v = srcw[wyk[k] * PR + wxk[k]];
-                    if (v != 0.0f) atomicAdd(&img[y * wl + x], v);      // one addition per cell and launch: deterministic (see below)
-                }
+                const bool in = wyk[k] >= 0 && (unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl;
+                const float v = in ? srcw[wyk[k] * PR + wxk[k]] : 0.0f;
+                red_add_if_nonzero(img + (in ? y * wl + x : 0), v);     // one addition per cell and launch: deterministic (see below)
             }
         }
         return;

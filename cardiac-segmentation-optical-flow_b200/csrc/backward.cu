@@ -130,12 +130,14 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
         // cooperative write-back of the (2r+2)^2 touched cells: a lane's cells are the same for every query, so their window coordinates
         // are computed once
         constexpr int TS = SIDE + 1, TCELLS = TS * TS, NIT = (TCELLS + 31) / 32;
-        int wyk[NIT], wxk[NIT];
+        int wyk[NIT], wxk[NIT], wofs[NIT], gofs[NIT];    // window row / column, offset inside the window, offset inside the level image
 #pragma unroll
         for (int k = 0; k < NIT; ++k) {
             const int c = lane + 32 * k;
-            wyk[k] = c < TCELLS ? 1 + c / TS : -1;
+            wyk[k] = c < TCELLS ? 1 + c / TS : -(1 << 20);   // a lane without a cell fails the row test below
             wxk[k] = 1 + c % TS;
+            wofs[k] = (1 + c / TS) * PR + wxk[k];
+            gofs[k] = (1 + c / TS) * wl + wxk[k];
         }
         const int nq = (int)min((long)kQ, P.N - n0);
         for (int q = 0; q < nq; ++q) {
@@ -143,14 +145,14 @@ __global__ void __launch_bounds__(32) lookup_bwd_kernel(const __grid_constant__ 
             if (qx == (1 << 30)) continue;
             float* img = P.glevel[l] + (size_t)(n0 + q) * hl * wl;
             const float* srcw = win + q * PITCH;
+            const int qbase = qy * wl + qx;
 #pragma unroll
             for (int k = 0; k < NIT; ++k) {
                 // branch-free: a predicated shared load and a predicated reduction (as `if`s each cell cost a divergence region of
                 // its own: BSSY / branch / BSYNC -- 5000 instructions per warp in a kernel that runs at its issue latency)
-                const int y = qy + wyk[k], x = qx + wxk[k];
-                const bool in = wyk[k] >= 0 && (unsigned)y < (unsigned)hl && (unsigned)x < (unsigned)wl;
-                const float v = in ? srcw[wyk[k] * PR + wxk[k]] : 0.0f;
-                red_add_if_nonzero(img + (in ? y * wl + x : 0), v);     // one addition per cell and launch: deterministic (see below)
+                const bool in = (unsigned)(qy + wyk[k]) < (unsigned)hl && (unsigned)(qx + wxk[k]) < (unsigned)wl;
+                const float v = in ? srcw[wofs[k]] : 0.0f;
+                red_add_if_nonzero(img + (in ? qbase + gofs[k] : 0), v);     // one addition per cell and launch: deterministic (see below)
             }
         }
         return;
